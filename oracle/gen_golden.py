@@ -1,0 +1,178 @@
+"""Generate golden vectors by running the REAL reference on CPU.  TEST INFRASTRUCTURE ONLY.
+
+Run in the build container only (needs the read-only checkout at /root/reference):
+
+    PYTHONDONTWRITEBYTECODE=1 python oracle/gen_golden.py
+
+Imports the reference with three import shims (oracle/ref_shims: package metadata, a stub
+``omegaconf`` and a stub ``pulp`` — none is called on this path) and writes
+``tests/golden/*.npz``.  Nothing in tests/, smoke() or bench.py reads /root/reference at run time:
+they read the committed ``.npz`` files.  bf16 / fp16 / fp8 arrays are stored as integer bit patterns.
+"""
+
+from __future__ import annotations
+
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = os.environ.get("MODELOPT_REFERENCE", "/root/reference")
+sys.path[:0] = [REF, os.path.join(HERE, "ref_shims")]
+sys.dont_write_bytecode = True
+warnings.filterwarnings("ignore")
+
+OUT = os.path.join(HERE, "..", "tests", "golden")
+
+_INT_VIEW = {torch.bfloat16: torch.int16, torch.float16: torch.int16, torch.float8_e4m3fn: torch.uint8}
+
+
+def to_np(t):
+    """Tensor -> numpy, low-precision float dtypes as integer bit patterns."""
+    if isinstance(t, (int, float)):
+        return np.asarray(t)
+    t = t.detach().cpu().contiguous()
+    if t.dtype in _INT_VIEW:
+        return t.view(_INT_VIEW[t.dtype]).numpy()
+    return t.numpy()
+
+
+DTYPES = {"f32": torch.float32, "f16": torch.float16, "bf16": torch.bfloat16}
+
+
+def gen_qdq():
+    from modelopt.torch.quantization.tensor_quant import fake_tensor_quant, scaled_e4m3
+
+    g = {}
+    torch.manual_seed(1234)
+    base = torch.randn(48, 256) * 3.0
+    base[3, 7] = 40.0  # outlier so clipping and saturation are exercised
+    base[5, :16] = 0.0
+    for dn, dt in DTYPES.items():
+        x = base.to(dt)
+        g[f"x_{dn}"] = to_np(x)
+        # ---------------- INT per-tensor -------------------------------------------------
+        for bits in (3, 4, 5, 7, 8, 11):
+            for unsigned in (False, True):
+                for narrow in (False, True):
+                    xi = x.abs() if unsigned else x
+                    amax = (xi.float().abs().max() * 0.7).to(dt)
+                    y = fake_tensor_quant(xi, amax, None, bits, unsigned, narrow)
+                    k = f"int_{dn}_b{bits}_u{int(unsigned)}_n{int(narrow)}"
+                    g[k + "_amax"], g[k + "_y"] = to_np(amax.float()), to_np(y)
+        # ---------------- INT per-channel / per-block ------------------------------------
+        for axis in (0, 1):
+            red = 1 - axis
+            amax = (x.float().abs().amax(dim=red, keepdim=True) * 0.9).to(dt)
+            y = fake_tensor_quant(x, amax, None, 8, False, False)
+            g[f"int_{dn}_axis{axis}_amax"], g[f"int_{dn}_axis{axis}_y"] = to_np(amax.float()), to_np(y)
+        xb = x.reshape(-1, 128)
+        amax = xb.float().abs().amax(dim=1, keepdim=True).to(dt)
+        y = fake_tensor_quant(xb, amax, None, 4, False, False)  # INT4 block-128 (INT4_AWQ_CFG)
+        g[f"int_{dn}_blk128_amax"], g[f"int_{dn}_blk128_y"] = to_np(amax.float()), to_np(y)
+        # tiny / zero amax conventions
+        for nm, am in (("tiny", 1e-26), ("zero", 0.0), ("eps", 1.0 / (1 << 24)), ("eps2", 1.5 / (1 << 24))):
+            y = fake_tensor_quant(x, torch.tensor(am), None, 8, False, False)
+            g[f"int_{dn}_{nm}_y"] = to_np(y)
+        # ---------------- FP8 --------------------------------------------------------------
+        for nm, am in (("max", x.float().abs().max()), ("clip", x.float().abs().max() * 0.5),
+                       ("zero", torch.tensor(0.0)), ("small", torch.tensor(1e-3))):
+            y = scaled_e4m3(x, am.to(dt), None, 4, 3)
+            g[f"fp8_{dn}_{nm}_amax"], g[f"fp8_{dn}_{nm}_y"] = to_np(am.to(dt).float()), to_np(y)
+        y = scaled_e4m3(x, None, None, 4, 3)
+        g[f"fp8_{dn}_none_y"] = to_np(y)
+        x3 = x.reshape(6, 8, 256)
+        for axis in (0, 1, 2):
+            red = [i for i in range(3) if i != axis]
+            amax = x3.float().abs().amax(dim=red, keepdim=True).to(dt)
+            y = scaled_e4m3(x3, amax, None, 4, 3)
+            g[f"fp8_{dn}_axis{axis}_amax"], g[f"fp8_{dn}_axis{axis}_y"] = to_np(amax.float()), to_np(y)
+    np.savez_compressed(os.path.join(OUT, "qdq_cpu.npz"), **g)
+    print("qdq_cpu.npz", len(g), "arrays")
+
+
+def gen_fp4_scales():
+    from modelopt.torch.kernels.quantization.gemm.fp4_kernel import compute_fp4_scales
+
+    g = {}
+    torch.manual_seed(7)
+    amax = (torch.randn(4096).abs() * 4.0)
+    amax[:8] = torch.tensor([0.0, 1e-8, 6.0 * 2**-11, 6.0 * 2**-10, 6.0, 448.0 * 6, 1e6, 3.3e-4])
+    g["amax"] = to_np(amax)
+    for nm, ga in (("auto", None), ("given", torch.tensor(17.0)), ("small", torch.tensor(1e-3))):
+        for q in (True, False):
+            for m in (448.0, 256.0):
+                s = compute_fp4_scales(amax, ga, q, m)
+                g[f"scale_{nm}_q{int(q)}_m{int(m)}"] = to_np(s)
+        if ga is not None:
+            g[f"ga_{nm}"] = to_np(ga)
+    np.savez_compressed(os.path.join(OUT, "fp4_scales_cpu.npz"), **g)
+    print("fp4_scales_cpu.npz", len(g), "arrays")
+
+
+def gen_amax():
+    from modelopt.torch.quantization.calib import MaxCalibrator
+    from modelopt.torch.quantization.utils import reduce_amax, reduce_block_amax
+
+    g = {}
+    torch.manual_seed(99)
+    for dn, dt in DTYPES.items():
+        xs = [(torch.randn(6, 40, 96) * (i + 1)).to(dt) for i in range(3)]
+        for i, x in enumerate(xs):
+            g[f"x{i}_{dn}"] = to_np(x)
+        g[f"amax_all_{dn}"] = to_np(reduce_amax(xs[0]).float())
+        for axis in (0, 1, 2, -1, (0, 2)):
+            an = str(axis).replace(" ", "").replace("(", "").replace(")", "").replace(",", "_")
+            c = MaxCalibrator(8, axis, False)
+            for x in xs:
+                c.collect(x)
+            g[f"calib_axis{an}_{dn}"] = to_np(c.compute_amax().float())
+        c = MaxCalibrator(8, None, False)
+        for x in xs:
+            c.collect(x)
+        g[f"calib_none_{dn}"] = to_np(c.compute_amax().float())
+        xb = xs[1].reshape(-1, 96)
+        g[f"blk16_{dn}"] = to_np(reduce_block_amax(xb, {-1: 16}).float())
+        g[f"blk32_{dn}"] = to_np(reduce_block_amax(xb, {-1: 32}).float())
+    np.savez_compressed(os.path.join(OUT, "amax_cpu.npz"), **g)
+    print("amax_cpu.npz", len(g), "arrays")
+
+
+def gen_nvfp4_pack():
+    from modelopt.torch.quantization.qtensor.nvfp4_tensor import NVFP4QTensor
+
+    g = {}
+    torch.manual_seed(2024)
+    base = torch.randn(32, 192) * 2.0
+    base[0, :16] = 0.0                       # zero block: scale 0 -> 1.0
+    base[1, :16] = base[1, :16] * 1e-6       # tiny block: scale clamps to 2^-9
+    base[2, :8] = torch.tensor([0.25, 0.75, 1.25, 1.75, 2.5, 3.5, 5.0, 6.0])
+    base[3, 5] = 300.0
+    for dn, dt in DTYPES.items():
+        x = base.to(dt)
+        g[f"x_{dn}"] = to_np(x)
+        qt, sf, sf2 = NVFP4QTensor.quantize(x.clone(), 16)
+        g[f"codes_{dn}"], g[f"sf_{dn}"], g[f"sf2_{dn}"] = to_np(qt._quantized_data), to_np(sf), to_np(sf2)
+        for fast in (False,):
+            d = qt.dequantize(dtype=dt, scale=sf, double_scale=sf2, block_sizes={-1: 16}, fast=fast)
+            g[f"deq_{dn}"] = to_np(d)
+        # externally supplied global scale (the quantizer's calibrated amax)
+        sf2b = torch.tensor(5.0) / (6.0 * 448.0)
+        qt, sf, _ = NVFP4QTensor.quantize(x.clone(), 16, weights_scaling_factor_2=sf2b)
+        g[f"codes_ext_{dn}"], g[f"sf_ext_{dn}"], g[f"sf2_ext_{dn}"] = to_np(qt._quantized_data), to_np(sf), to_np(sf2b)
+        # ragged last dim (padded to the block)
+        xr = x[:, :184].contiguous()
+        qt, sf, sf2 = NVFP4QTensor.quantize(xr.clone(), 16)
+        g[f"codes_rag_{dn}"], g[f"sf_rag_{dn}"], g[f"sf2_rag_{dn}"] = to_np(qt._quantized_data), to_np(sf), to_np(sf2)
+    np.savez_compressed(os.path.join(OUT, "nvfp4_pack_cpu.npz"), **g)
+    print("nvfp4_pack_cpu.npz", len(g), "arrays")
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack"]
+    for w in which:
+        globals()["gen_" + w]()
