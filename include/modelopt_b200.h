@@ -1,0 +1,138 @@
+/* modelopt_b200 — C ABI of the B200 (sm_100a) quantization hot path.
+ *
+ * Drop-in boundary for ModelOpt's TensorQuantizer hot path: these are the entry points the
+ * reference's Python binds today through three JIT-compiled pybind extensions and a set of Triton
+ * kernels.  Each declaration cites the reference interface it replaces (paths relative to the
+ * reference checkout).  No torch types cross this boundary: plain pointers, sizes, a dtype code and
+ * a `cudaStream_t` passed as `void*`.  Unless a name ends in `_host`, every data pointer is a DEVICE
+ * pointer valid on the current CUDA device and the call only enqueues work on `stream` (no
+ * host-device synchronisation).  `_host` entry points take HOST pointers, stage through pinned
+ * buffers owned by the library and return after the result is back in host memory.
+ *
+ * Return value: 0 on success; MO_ERR_* (<0) for a rejected argument; a positive `cudaError_t`
+ * otherwise.  `mo_last_error()` returns a thread-local description of the last failure.
+ */
+#ifndef MODELOPT_B200_H_
+#define MODELOPT_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MO_ABI_VERSION 1
+
+typedef enum { MO_F32 = 0, MO_F16 = 1, MO_BF16 = 2 } mo_dtype;
+
+enum {
+  MO_OK = 0,
+  MO_ERR_DTYPE = -1,    /* unsupported dtype code */
+  MO_ERR_SHAPE = -2,    /* inconsistent sizes */
+  MO_ERR_ARG = -3,      /* bad scalar argument (num_bits, block size, ...) */
+  MO_ERR_NULL = -4,     /* required pointer is NULL */
+  MO_ERR_ALIGN = -5,    /* pointer not aligned to the element size */
+  MO_ERR_NO_DEVICE = -6 /* no sm_100 device / driver */
+};
+
+/* Bits OR-ed into the optional device status word by kernels that can detect bad input. */
+#define MO_FLAG_NEGATIVE_IN_UNSIGNED 1u /* tensor_quant_gpu.cu:65-67 CUDA_KERNEL_ASSERT(inputs >= 0) */
+#define MO_FLAG_NEGATIVE_AMAX 2u        /* tensor_quant_gpu.cu:44   CUDA_KERNEL_ASSERT(amax >= 0)   */
+
+/* NVFP4 division numerics. */
+#define MO_DIV_TRITON 0 /* div.full.f32 — what the reference's Triton kernels execute on sm_100a */
+#define MO_DIV_IEEE 1   /* div.rn.f32  — matches the CPU oracle / the torch packer arithmetic    */
+
+int mo_abi_version(void);
+const char* mo_last_error(void);
+/* Name of device 0, its SM count and compute capability (major*10+minor); MO_ERR_NO_DEVICE if none. */
+int mo_device_info(char* name, int name_len, int* sm_count, int* cc);
+
+/* ------------------------------------------------------------------------------------------------
+ * Fake quantize-dequantize (row a1-a4 of SURVEY.md section 8).
+ *
+ * Tensors are contiguous with `n` elements.  Per-tensor: amax has 1 element (axis_size = 1,
+ * inner = n).  Per-axis / per-block: the tensor is viewed [outer, axis_size, inner] and element
+ * idx uses amax[(idx / inner) % axis_size]; the reference's INT4 block-128 path is the view
+ * [n/128, 128] with axis_size = n/128, inner = 128 (tensor_quant.py:107-111).
+ * `amax` is fp32 on the device (the reference converts with amax.to(float), tensor_quant_gpu.cu:83).
+ * In-place (y == x) is allowed.
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Replaces cuda_ext.fake_tensor_quant / fake_tensor_quant_with_axis / fake_tensor_quant_
+ * (gemm/tensor_quant.cpp:36-62, gemm/tensor_quant_gpu.cu:58-140).
+ * status: optional device uint32 that receives MO_FLAG_* bits (may be NULL). */
+int mo_qdq_int(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
+               int64_t inner, int num_bits, int is_unsigned, int narrow_range, uint32_t* status,
+               void* stream);
+
+/* Replaces cuda_ext_fp8.fake_e4m3fy / fake_e4m3fy_with_axis (gemm/tensor_quant_gpu_fp8.cu:35-107)
+ * including the host-side torch ops that build scale = 448/amax and inv_scale = 1/scale (:93-98).
+ * amax == NULL: plain cast through E4M3 (tensor_quant.py:46-59 with amax=None). */
+int mo_qdq_fp8(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
+               int64_t inner, void* stream);
+
+/* Replaces Triton fp4_fake_quant_block (gemm/fp4_kernel_hopper.py:102-170): dynamic NVFP4 over the
+ * last dim of a [rows, cols] view; `global_amax` is the calibrated fp32 scalar (device).
+ * block in {16, 32, 64}; a ragged last block is zero-padded like the reference's tile loads. */
+int mo_qdq_nvfp4_dynamic(const void* x, void* y, int64_t rows, int64_t cols, int dtype,
+                         const float* global_amax, int block, int div_mode, void* stream);
+
+/* Replaces Triton static_blockwise_fp4_fake_quant_kernel (gemm/fp4_kernel.py:193-214, scalar math
+ * common/nvfp4_quant.py:66-101): x is n_blocks*block contiguous elements, `scale` is the fp32
+ * per-block scale (device) as produced by compute_fp4_scales (:217-251; see mo_fp4_scales). */
+int mo_qdq_nvfp4_static(const void* x, void* y, int64_t n_blocks, int block, int in_dtype,
+                        int out_dtype, const float* scale, int div_mode, void* stream);
+
+/* Replaces compute_fp4_scales (gemm/fp4_kernel.py:217-251): scale = amax/6, optionally round-tripped
+ * through E4M3 under scale_amax = global_amax*(448/fp8_max)/6.  global_amax == NULL: reduce it from
+ * `amax` first (two launches).  amax/scale fp32 device arrays of n_blocks. */
+int mo_fp4_scales(const float* amax, float* scale, int64_t n_blocks, const float* global_amax,
+                  int quantize_block_scales, float fp8_max_for_normalization, int div_mode,
+                  uint32_t* scratch /* 4-byte device word, needed only when global_amax == NULL */,
+                  void* stream);
+
+/* Replaces Triton static_blockwise_fp4_cast_kernel (gemm/fp4_kernel.py:319-400). */
+int mo_fp4_cast(const void* x, void* y, int64_t n, int in_dtype, int out_dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Amax reductions (rows a7, a8): replaces reduce_amax / reduce_block_amax
+ * (quantization/utils/core_utils.py:43-89, :146-183) and the running max of MaxCalibrator.collect
+ * (calib/max.py:52-86).
+ *
+ * The tensor is viewed [outer, axis_size, inner]; out[a] = max over (o, i) of |x[o, a, i]|, MERGED
+ * into `amax_bits` with an unsigned max on the fp32 bit pattern (one atomic per CTA and channel).
+ * The caller zero-fills amax_bits before the first batch and reinterprets it as fp32 afterwards:
+ * max is exact and order-independent, NaN inputs survive as a NaN pattern (torch.max semantics) and
+ * inf as inf, so the reference's three host-syncing asserts (max.py:69-77) become one check at
+ * finish time.  Per-tensor: axis_size = 1.
+ * ---------------------------------------------------------------------------------------------- */
+int mo_amax(const void* x, int64_t outer, int64_t axis_size, int64_t inner, int dtype,
+            uint32_t* amax_bits, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
+ * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.
+ * ---------------------------------------------------------------------------------------------- */
+/* cvt.rn.satfinite.e2m1x2.f32 round trip == the reference compare chain, over all 2^31 |fp32|. */
+int mo_selftest_e2m1(uint64_t* mismatches);
+/* ExactDiv (hoisted reciprocal) == div.rn.f32 for q in [-q_max, q_max] x n_scales random scales. */
+int mo_selftest_exact_div(int q_max, int n_scales, uint64_t seed, uint64_t* mismatches);
+
+/* ------------------------------------------------------------------------------------------------
+ * HOST-buffer entry points (the end-to-end path bench.py reports as `e2e`).  x/y are host pointers
+ * (pinned or pageable); the call stages chunks through library-owned pinned buffers on two streams
+ * so H2D, the kernel and D2H overlap, and returns when y is complete.
+ * ---------------------------------------------------------------------------------------------- */
+int mo_qdq_fp8_host(const void* x, void* y, int64_t n, int dtype, float amax);
+int mo_qdq_int_host(const void* x, void* y, int64_t n, int dtype, float amax, int num_bits,
+                    int is_unsigned, int narrow_range);
+int mo_qdq_nvfp4_dynamic_host(const void* x, void* y, int64_t rows, int64_t cols, int dtype,
+                              float global_amax, int block, int div_mode);
+/* amax of a host tensor (per-tensor); *amax_out receives the fp32 value. */
+int mo_amax_host(const void* x, int64_t n, int dtype, float* amax_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MODELOPT_B200_H_ */

@@ -1,0 +1,276 @@
+"""Tensor-level wrappers over the C ABI: validate, pick pointers/sizes/stream, call.  torch is only
+plumbing here (device memory, current stream); all arithmetic happens in libmodelopt_b200.so."""
+
+from __future__ import annotations
+
+import math
+import os
+
+import torch
+
+from . import _lib
+from ._lib import MO_BF16, MO_DIV_IEEE, MO_DIV_TRITON, MO_F16, MO_F32, check
+
+_DT = {torch.float32: MO_F32, torch.float16: MO_F16, torch.bfloat16: MO_BF16}
+
+
+def default_numerics() -> int:
+    """NVFP4 numerics mode: 'triton' (what the reference runs on a GPU, default) or 'ieee'."""
+    return MO_DIV_IEEE if os.environ.get("MODELOPT_B200_NUMERICS", "triton").lower() == "ieee" else MO_DIV_TRITON
+
+
+def _mode(numerics) -> int:
+    if numerics is None:
+        return default_numerics()
+    if isinstance(numerics, str):
+        return MO_DIV_IEEE if numerics.lower() == "ieee" else MO_DIV_TRITON
+    return int(numerics)
+
+
+def _code(t: torch.Tensor) -> int:
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError(f"modelopt_b200: unsupported dtype {t.dtype} (float32/float16/bfloat16 only)") from None
+
+
+def _cuda(t: torch.Tensor, what: str):
+    if not t.is_cuda:
+        raise RuntimeError(
+            f"modelopt_b200.{what}: expected a CUDA tensor, got {t.device}. This package is the B200 CUDA path "
+            "only; there is no CPU fallback."
+        )
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+class _dev:
+    """Make t's device current for the duration of the call (cheap no-op when it already is)."""
+
+    def __init__(self, t):
+        self.idx = t.device.index
+        self.prev = None
+
+    def __enter__(self):
+        cur = torch.cuda.current_device()
+        if self.idx is not None and self.idx != cur:
+            self.prev = cur
+            torch.cuda.set_device(self.idx)
+
+    def __exit__(self, *a):
+        if self.prev is not None:
+            torch.cuda.set_device(self.prev)
+
+
+def _f32_vec(a: torch.Tensor, like: torch.Tensor) -> torch.Tensor:
+    """amax -> flat fp32 on like.device (reference: amax.to(float), tensor_quant_gpu.cu:83)."""
+    a = a.detach()
+    if a.device != like.device:
+        a = a.to(like.device)
+    if a.dtype != torch.float32:
+        a = a.to(torch.float32)
+    return a.contiguous().reshape(-1)
+
+
+def _axis_of(x: torch.Tensor, amax: torch.Tensor):
+    """(axis_size, inner) for a scalar or single-axis amax (tensor_quant.py:105-111); else ValueError."""
+    n = amax.numel()
+    if n == 1:
+        return 1, x.numel()
+    shape = list(amax.shape)
+    if amax.dim() == x.dim() and shape.count(1) == x.dim() - 1:
+        axis = shape.index(n)
+    elif amax.dim() == 1:
+        axis = list(x.shape).index(n)  # 1-D amax: first dim of that size (reference squeezes first)
+    else:
+        raise ValueError(f"amax of shape {tuple(amax.shape)} is not a scalar or a single-axis vector")
+    if x.shape[axis] != n:
+        raise ValueError(f"amax has {n} elements but input dim {axis} has {x.shape[axis]}")
+    return n, math.prod(x.shape[axis + 1:])
+
+
+def _via_f32(fn, x, *a, **k):
+    """float64 input: the reference kernels compute on (float)x and cast back (tensor_quant_gpu.cu:72)."""
+    return fn(x.to(torch.float32), *a, **k).to(torch.float64)
+
+
+# ------------------------------------------------------------------------------------------------
+def qdq_int(x, amax, num_bits=8, unsigned=False, narrow_range=True, out=None, status=None):
+    _cuda(x, "qdq_int")
+    if x.dtype == torch.float64:
+        return _via_f32(qdq_int, x, amax, num_bits, unsigned, narrow_range, None, status)
+    x = x.contiguous()
+    axis_size, inner = _axis_of(x, amax)
+    am = _f32_vec(amax, x)
+    y = torch.empty_like(x) if out is None else out
+    with _dev(x):
+        check(_lib.load().mo_qdq_int(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), am.data_ptr(), axis_size,
+                                     inner, int(num_bits), int(bool(unsigned)), int(bool(narrow_range)),
+                                     status.data_ptr() if status is not None else None, _stream(x)), "mo_qdq_int")
+    return y
+
+
+def qdq_fp8(x, amax=None, out=None):
+    _cuda(x, "qdq_fp8")
+    if x.dtype == torch.float64:
+        return _via_f32(qdq_fp8, x, amax)
+    x = x.contiguous()
+    y = torch.empty_like(x) if out is None else out
+    if amax is None:
+        axis_size, inner, ap, am = 1, x.numel(), None, None
+    else:
+        axis_size, inner = _axis_of(x, amax)
+        am = _f32_vec(amax, x)
+        ap = am.data_ptr()
+    with _dev(x):
+        check(_lib.load().mo_qdq_fp8(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), ap, axis_size, inner,
+                                     _stream(x)), "mo_qdq_fp8")
+    return y
+
+
+def qdq_nvfp4_dynamic(x, global_amax, block=16, numerics=None, out=None):
+    _cuda(x, "qdq_nvfp4_dynamic")
+    if x.numel() == 0:
+        return x.clone()
+    x = x.contiguous()
+    cols = x.shape[-1]
+    rows = x.numel() // cols
+    ga = _f32_vec(global_amax, x)
+    if ga.numel() != 1:
+        ga = ga.amax().reshape(1)  # tensor_quant.py:173-174
+    y = torch.empty_like(x) if out is None else out
+    with _dev(x):
+        check(_lib.load().mo_qdq_nvfp4_dynamic(x.data_ptr(), y.data_ptr(), rows, cols, _code(x), ga.data_ptr(),
+                                               int(block), _mode(numerics), _stream(x)), "mo_qdq_nvfp4_dynamic")
+    return y
+
+
+def fp4_scales(amax, global_amax=None, quantize_block_scales=True, fp8_max_for_normalization=448.0, numerics=None):
+    _cuda(amax, "fp4_scales")
+    am = _f32_vec(amax, amax)
+    scale = torch.empty_like(am)
+    ga = _f32_vec(global_amax, amax) if global_amax is not None else None
+    scratch = torch.empty(1, dtype=torch.int32, device=amax.device) if (ga is None and quantize_block_scales) else None
+    with _dev(amax):
+        check(_lib.load().mo_fp4_scales(am.data_ptr(), scale.data_ptr(), am.numel(),
+                                        ga.data_ptr() if ga is not None else None, int(bool(quantize_block_scales)),
+                                        float(fp8_max_for_normalization), _mode(numerics),
+                                        scratch.data_ptr() if scratch is not None else None, _stream(amax)),
+              "mo_fp4_scales")
+    return scale.reshape(amax.shape)
+
+
+def qdq_nvfp4_static(x, amax, global_amax=None, quantize_block_scales=True, fp8_max_for_normalization=448.0,
+                     out_dtype=None, numerics=None):
+    _cuda(x, "qdq_nvfp4_static")
+    nb = amax.numel()
+    if nb == 0 or x.numel() % nb != 0:
+        raise ValueError(
+            f"x.numel() ({x.numel()}) is not divisible by amax.numel() ({nb}); "
+            "they must satisfy x.numel() == NUM_FP4_BLOCKS * BLOCK_SIZE."
+        )
+    block = x.numel() // nb
+    out_dtype = out_dtype or x.dtype
+    scale = fp4_scales(amax, global_amax, quantize_block_scales, fp8_max_for_normalization, numerics)
+    x = x.contiguous()
+    y = torch.empty(x.shape, dtype=out_dtype, device=x.device)
+    with _dev(x):
+        check(_lib.load().mo_qdq_nvfp4_static(x.data_ptr(), y.data_ptr(), nb, block, _code(x), _code(y),
+                                              scale.data_ptr(), _mode(numerics), _stream(x)), "mo_qdq_nvfp4_static")
+    return y
+
+
+def fp4_cast(x, out_dtype=None):
+    _cuda(x, "fp4_cast")
+    x = x.contiguous()
+    y = torch.empty(x.shape, dtype=out_dtype or x.dtype, device=x.device)
+    with _dev(x):
+        check(_lib.load().mo_fp4_cast(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), _code(y), _stream(x)),
+              "mo_fp4_cast")
+    return y
+
+
+# ------------------------------------------------------------------------------------------------
+def amax_into(x, outer, axis_size, inner, bits):
+    """Merge max|x| over the [outer, axis_size, inner] view into `bits` (int32 view of fp32 amax)."""
+    _cuda(x, "amax_into")
+    assert bits.numel() == axis_size and bits.element_size() == 4 and bits.is_contiguous()
+    x = x.contiguous()
+    with _dev(x):
+        check(_lib.load().mo_amax(x.data_ptr(), outer, axis_size, inner, _code(x), bits.data_ptr(), _stream(x)),
+              "mo_amax")
+
+
+def _collapse_keep_axes(shape, keep):
+    """View a contiguous tensor as [outer, axis, inner] keeping the (contiguous run of) dims in `keep`."""
+    keep = sorted(keep)
+    if not keep:
+        return 1, 1, math.prod(shape)
+    # drop size-1 dims from consideration: they are free to sit on either side
+    eff = [d for d in keep if shape[d] != 1]
+    if not eff:
+        return 1, 1, math.prod(shape)
+    lo, hi = eff[0], eff[-1]
+    for d in range(lo, hi + 1):
+        if d not in keep and shape[d] != 1:
+            return None  # kept dims are not adjacent
+    return math.prod(shape[:lo]), math.prod(shape[lo:hi + 1]), math.prod(shape[hi + 1:])
+
+
+def reduce_amax(x, axis=None, keepdims=True, squeeze_scalar=True):
+    """reduce_amax (core_utils.py:146-183) in one read; `axis` = dims to REDUCE; result in x.dtype."""
+    _cuda(x, "reduce_amax")
+    if x.dtype in (torch.float8_e4m3fn, torch.float8_e5m2):
+        x = x.to(torch.get_default_dtype())
+    if x.dtype == torch.float64:
+        return reduce_amax(x.float(), axis, keepdims, squeeze_scalar).double()  # exact unless |x| > fp32 range
+    nd = x.dim()
+    if axis is None:
+        red = list(range(nd))
+    else:
+        red = [axis] if isinstance(axis, int) else list(axis)
+        red = sorted({a % nd for a in red}) if nd else []
+    keep = [d for d in range(nd) if d not in red]
+    x = x.contiguous()
+    view = _collapse_keep_axes(list(x.shape), keep)
+    if view is None:
+        # kept dims not adjacent: move them together (one extra copy; rare, e.g. axis=(0, 2) of a 3-D tensor)
+        perm = keep + red
+        xp = x.permute(perm).contiguous()
+        out = reduce_amax(xp, list(range(len(keep), nd)), keepdims=False, squeeze_scalar=False)
+        if keepdims:
+            out = out.reshape([x.shape[d] if d in keep else 1 for d in range(nd)])
+        if squeeze_scalar and out.numel() == 1:
+            out = out.squeeze()
+        return out
+    outer, axis_size, inner = view
+    bits = torch.zeros(axis_size, dtype=torch.int32, device=x.device)
+    if x.numel():
+        amax_into(x, outer, axis_size, inner, bits)
+    out = bits.view(torch.float32).to(x.dtype)
+    if axis is None:
+        return out.reshape(())
+    if keepdims:
+        out = out.reshape([x.shape[d] if d in keep else 1 for d in range(nd)])
+    else:
+        out = out.reshape([x.shape[d] for d in keep])
+    if squeeze_scalar and out.numel() == 1:
+        out = out.squeeze()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
+def selftest_e2m1() -> int:
+    import ctypes as C
+    n = C.c_uint64(0)
+    check(_lib.load().mo_selftest_e2m1(C.byref(n)), "mo_selftest_e2m1")
+    return n.value
+
+
+def selftest_exact_div(q_max=65536, n_scales=4096, seed=0) -> int:
+    import ctypes as C
+    n = C.c_uint64(0)
+    check(_lib.load().mo_selftest_exact_div(q_max, n_scales, seed, C.byref(n)), "mo_selftest_exact_div")
+    return n.value

@@ -1,0 +1,95 @@
+"""Kernel micro-benchmark: GB/s of each product kernel on BASELINE shapes (CUDA events, L2-exceeding
+inputs), and — when oracle/_ref holds the reference — the reference's own GPU kernels beside them."""
+
+from __future__ import annotations
+
+import json
+import os
+import sys
+import warnings
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tensorrt-model-optimizer_b200")]
+warnings.filterwarnings("ignore")
+from modelopt_b200 import ops  # noqa: E402
+
+PEAK = 6544.3
+try:
+    PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:  # noqa: BLE001
+    pass
+
+
+def timeit(fn, iters=20, warm=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(iters)]
+    for a, b in ev:
+        a.record(); fn(); b.record()
+    torch.cuda.synchronize()
+    ts = sorted(a.elapsed_time(b) for a, b in ev)
+    return ts[len(ts) // 2], ts[0]
+
+
+def report(name, nbytes, fn):
+    med, best = timeit(fn)
+    print(f"{name:46s} {med:8.3f} ms  {nbytes / med / 1e6:8.1f} GB/s  ({nbytes / med / 1e6 / PEAK * 100:5.1f}% of {PEAK:.0f})"
+          f"   best {nbytes / best / 1e6:8.1f}", flush=True)
+
+
+def main():
+    shapes = [(16384, 4096), (16384, 14336)] if len(sys.argv) < 2 else [tuple(map(int, sys.argv[1].split("x")))]
+    for shape in shapes:
+        x = torch.randn(shape, device="cuda", dtype=torch.bfloat16)
+        y = torch.empty_like(x)
+        n = x.numel()
+        am = ops.reduce_amax(x).float()
+        print(f"--- bf16 {shape}  ({n * 2 / 1e6:.0f} MB)")
+        report("copy (torch y.copy_(x))", 4 * n, lambda: y.copy_(x))
+        report("amax per-tensor", 2 * n, lambda: ops.reduce_amax(x))
+        report("amax per-row (axis 0 kept)", 2 * n, lambda: ops.reduce_amax(x, axis=1))
+        report("amax per-col (last axis kept)", 2 * n, lambda: ops.reduce_amax(x, axis=0))
+        report("amax block-128", 2 * n, lambda: ops.reduce_amax(x.view(-1, 128), axis=1))
+        report("qdq fp8 per-tensor", 4 * n, lambda: ops.qdq_fp8(x, am, out=y))
+        report("qdq int8 per-tensor", 4 * n, lambda: ops.qdq_int(x, am, 8, False, False, out=y))
+        amc = ops.reduce_amax(x, axis=1).float()
+        report("qdq int8 per-channel", 4 * n, lambda: ops.qdq_int(x, amc, 8, False, False, out=y))
+        xb = x.view(-1, 128)
+        amb = ops.reduce_amax(xb, axis=1).float()
+        report("qdq int4 block-128", 4 * n, lambda: ops.qdq_int(xb, amb, 4, False, False, out=y.view(-1, 128)))
+        report("qdq nvfp4 dynamic (triton numerics)", 4 * n, lambda: ops.qdq_nvfp4_dynamic(x, am, 16, "triton", out=y))
+        report("qdq nvfp4 dynamic (ieee numerics)", 4 * n, lambda: ops.qdq_nvfp4_dynamic(x, am, 16, "ieee", out=y))
+        bam = ops.reduce_amax(x.view(-1, 16), axis=1).float()
+        sc = ops.fp4_scales(bam, am, True)
+        report("qdq nvfp4 static (scales given)", 4.25 * n, lambda: ops.qdq_nvfp4_static(x.view(-1, 16), bam, am))
+        del y
+        ref = os.path.join(ROOT, "oracle", "_ref")
+        if os.path.isdir(os.path.join(ref, "modelopt")):
+            sys.path[:0] = [ref, os.path.join(ROOT, "oracle", "ref_shims")]
+            try:
+                import modelopt.torch.kernels.quantization.gemm as tk
+                from modelopt.torch.quantization.calib import MaxCalibrator
+                from modelopt.torch.quantization.tensor_quant import fake_tensor_quant, scaled_e4m3
+                from modelopt.torch.quantization.utils import reduce_amax as ref_amax
+
+                report("REF triton fp4_fake_quant_block", 4 * n, lambda: tk.fp4_fake_quant_block(x, am))
+                report("REF reduce_amax", 2 * n, lambda: ref_amax(x))
+                report("REF MaxCalibrator.collect", 2 * n, lambda: MaxCalibrator(8, None, False).collect(x))
+                try:
+                    report("REF scaled_e4m3 (JIT ext)", 4 * n, lambda: scaled_e4m3(x, am, None, 4, 3))
+                    report("REF fake_tensor_quant int8 (JIT ext)", 4 * n, lambda: fake_tensor_quant(x, am, None, 8, False, False))
+                    report("REF fake_tensor_quant int8 per-channel", 4 * n,
+                           lambda: fake_tensor_quant(x, amc.unsqueeze(1), None, 8, False, False))
+                except Exception as e:  # noqa: BLE001
+                    print("REF JIT ext failed:", repr(e)[:200])
+            except Exception as e:  # noqa: BLE001
+                print("REF import failed:", repr(e)[:300])
+        del x
+        torch.cuda.empty_cache()
+
+
+if __name__ == "__main__":
+    main()
