@@ -97,7 +97,7 @@ def main():
     # informational: compare the product kernels right away
     try:
         from modelopt_b200 import ops
-        from tests.conftest import from_np
+        sys.path.insert(0, os.path.join(ROOT, "tests")); from conftest import from_np
 
         for k in sorted(g):
             if not k.startswith("y_"):

@@ -13,6 +13,14 @@ from ._lib import MO_BF16, MO_DIV_IEEE, MO_DIV_TRITON, MO_F16, MO_F32, check
 
 _DT = {torch.float32: MO_F32, torch.float16: MO_F16, torch.bfloat16: MO_BF16}
 
+# kernels enqueued through the C ABI since import (bench.py reports the delta as `gpu_launches`)
+LAUNCHES = [0]
+
+
+def _launched(rc, what, n=1):
+    check(rc, what)
+    LAUNCHES[0] += n
+
 
 def default_numerics() -> int:
     """NVFP4 numerics mode: 'triton' (what the reference runs on a GPU, default) or 'ieee'."""
@@ -106,7 +114,7 @@ def qdq_int(x, amax, num_bits=8, unsigned=False, narrow_range=True, out=None, st
     am = _f32_vec(amax, x)
     y = torch.empty_like(x) if out is None else out
     with _dev(x):
-        check(_lib.load().mo_qdq_int(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), am.data_ptr(), axis_size,
+        _launched(_lib.load().mo_qdq_int(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), am.data_ptr(), axis_size,
                                      inner, int(num_bits), int(bool(unsigned)), int(bool(narrow_range)),
                                      status.data_ptr() if status is not None else None, _stream(x)), "mo_qdq_int")
     return y
@@ -125,7 +133,7 @@ def qdq_fp8(x, amax=None, out=None):
         am = _f32_vec(amax, x)
         ap = am.data_ptr()
     with _dev(x):
-        check(_lib.load().mo_qdq_fp8(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), ap, axis_size, inner,
+        _launched(_lib.load().mo_qdq_fp8(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), ap, axis_size, inner,
                                      _stream(x)), "mo_qdq_fp8")
     return y
 
@@ -142,7 +150,7 @@ def qdq_nvfp4_dynamic(x, global_amax, block=16, numerics=None, out=None):
         ga = ga.amax().reshape(1)  # tensor_quant.py:173-174
     y = torch.empty_like(x) if out is None else out
     with _dev(x):
-        check(_lib.load().mo_qdq_nvfp4_dynamic(x.data_ptr(), y.data_ptr(), rows, cols, _code(x), ga.data_ptr(),
+        _launched(_lib.load().mo_qdq_nvfp4_dynamic(x.data_ptr(), y.data_ptr(), rows, cols, _code(x), ga.data_ptr(),
                                                int(block), _mode(numerics), _stream(x)), "mo_qdq_nvfp4_dynamic")
     return y
 
@@ -154,7 +162,7 @@ def fp4_scales(amax, global_amax=None, quantize_block_scales=True, fp8_max_for_n
     ga = _f32_vec(global_amax, amax) if global_amax is not None else None
     scratch = torch.empty(1, dtype=torch.int32, device=amax.device) if (ga is None and quantize_block_scales) else None
     with _dev(amax):
-        check(_lib.load().mo_fp4_scales(am.data_ptr(), scale.data_ptr(), am.numel(),
+        _launched(_lib.load().mo_fp4_scales(am.data_ptr(), scale.data_ptr(), am.numel(),
                                         ga.data_ptr() if ga is not None else None, int(bool(quantize_block_scales)),
                                         float(fp8_max_for_normalization), _mode(numerics),
                                         scratch.data_ptr() if scratch is not None else None, _stream(amax)),
@@ -177,7 +185,7 @@ def qdq_nvfp4_static(x, amax, global_amax=None, quantize_block_scales=True, fp8_
     x = x.contiguous()
     y = torch.empty(x.shape, dtype=out_dtype, device=x.device)
     with _dev(x):
-        check(_lib.load().mo_qdq_nvfp4_static(x.data_ptr(), y.data_ptr(), nb, block, _code(x), _code(y),
+        _launched(_lib.load().mo_qdq_nvfp4_static(x.data_ptr(), y.data_ptr(), nb, block, _code(x), _code(y),
                                               scale.data_ptr(), _mode(numerics), _stream(x)), "mo_qdq_nvfp4_static")
     return y
 
@@ -187,7 +195,7 @@ def fp4_cast(x, out_dtype=None):
     x = x.contiguous()
     y = torch.empty(x.shape, dtype=out_dtype or x.dtype, device=x.device)
     with _dev(x):
-        check(_lib.load().mo_fp4_cast(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), _code(y), _stream(x)),
+        _launched(_lib.load().mo_fp4_cast(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), _code(y), _stream(x)),
               "mo_fp4_cast")
     return y
 
@@ -199,7 +207,7 @@ def amax_into(x, outer, axis_size, inner, bits):
     assert bits.numel() == axis_size and bits.element_size() == 4 and bits.is_contiguous()
     x = x.contiguous()
     with _dev(x):
-        check(_lib.load().mo_amax(x.data_ptr(), outer, axis_size, inner, _code(x), bits.data_ptr(), _stream(x)),
+        _launched(_lib.load().mo_amax(x.data_ptr(), outer, axis_size, inner, _code(x), bits.data_ptr(), _stream(x)),
               "mo_amax")
 
 
@@ -274,3 +282,55 @@ def selftest_exact_div(q_max=65536, n_scales=4096, seed=0) -> int:
     n = C.c_uint64(0)
     check(_lib.load().mo_selftest_exact_div(q_max, n_scales, seed, C.byref(n)), "mo_selftest_exact_div")
     return n.value
+
+
+# ------------------------------------------------------------------------------------------------
+# HOST-buffer entry points (x / y are CPU tensors, ideally pinned): H2D -> kernel -> D2H inside the call.
+# ------------------------------------------------------------------------------------------------
+def _host(t: torch.Tensor, what: str):
+    if t.is_cuda or not t.is_contiguous():
+        raise RuntimeError(f"modelopt_b200.{what}: expected a contiguous CPU tensor")
+
+
+def _chunks(x):
+    return max(1, -(-x.numel() * x.element_size() // (32 << 20)))
+
+
+def amax_host(x: torch.Tensor) -> float:
+    """max|x| of a host tensor (streams it through the GPU)."""
+    import ctypes as C
+
+    _host(x, "amax_host")
+    out = C.c_float(0.0)
+    _launched(_lib.load().mo_amax_host(x.data_ptr(), x.numel(), _code(x), C.byref(out)), "mo_amax_host",
+              n=_chunks(x))
+    return out.value
+
+
+def qdq_fp8_host(x: torch.Tensor, amax: float, out: torch.Tensor | None = None) -> torch.Tensor:
+    _host(x, "qdq_fp8_host")
+    y = torch.empty_like(x) if out is None else out
+    _launched(_lib.load().mo_qdq_fp8_host(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), float(amax)),
+              "mo_qdq_fp8_host", n=_chunks(x))
+    return y
+
+
+def qdq_int_host(x: torch.Tensor, amax: float, num_bits=8, unsigned=False, narrow_range=True,
+                 out: torch.Tensor | None = None) -> torch.Tensor:
+    _host(x, "qdq_int_host")
+    y = torch.empty_like(x) if out is None else out
+    _launched(_lib.load().mo_qdq_int_host(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), float(amax),
+                                          int(num_bits), int(bool(unsigned)), int(bool(narrow_range))),
+              "mo_qdq_int_host", n=_chunks(x))
+    return y
+
+
+def qdq_nvfp4_dynamic_host(x: torch.Tensor, global_amax: float, block=16, numerics=None,
+                           out: torch.Tensor | None = None) -> torch.Tensor:
+    _host(x, "qdq_nvfp4_dynamic_host")
+    y = torch.empty_like(x) if out is None else out
+    cols = x.shape[-1]
+    _launched(_lib.load().mo_qdq_nvfp4_dynamic_host(x.data_ptr(), y.data_ptr(), x.numel() // cols, cols, _code(x),
+                                                    float(global_amax), int(block), _mode(numerics)),
+              "mo_qdq_nvfp4_dynamic_host", n=_chunks(x))
+    return y

@@ -314,3 +314,55 @@ def test_full_size_properties(ops):
     assert bits_equal(y[rows.cuda()].cpu(), want)
     y8 = ops.qdq_fp8(x, am)
     assert bits_equal(y8[rows.cuda()].cpu(), ofq.fp8_qdq(x[rows.cuda()].cpu(), am.cpu()))
+
+
+# ---------------------------------------------------------------------------------------- reference GPU kernels
+# tests/golden/nvfp4_triton_b200.npz holds outputs of the reference's OWN compiled kernels captured on a B200
+# (oracle/gen_golden_gpu.py): Triton fp4_fake_quant_block / static_blockwise_fp4_fake_quant /
+# compute_fp4_scales and the JIT CUDA extensions fake_e4m3fy / fake_tensor_quant[_with_axis].
+# This is the comparison that pins the div.full.f32 step ("triton" numerics).  Bar: bit-exact.
+def _same_bits(a, b):
+    iv = torch.int32 if a.dtype == torch.float32 else torch.int16
+    return int((a.contiguous().view(iv) != b.contiguous().view(iv)).sum())
+
+
+@pytest.mark.parametrize("dn", list(DTYPES))
+def test_reference_triton_nvfp4_dynamic_bit_exact(ops, dn):
+    g = load_golden("nvfp4_triton_b200.npz")
+    dt = DTYPES[dn]
+    for nm in ("rand", "adv"):
+        x = from_np(g[f"x_{nm}_{dn}"], dt)
+        for an in ("max", "clip"):
+            ga = torch.from_numpy(g[f"ga_{nm}_{an}_{dn}"])
+            got = ops.qdq_nvfp4_dynamic(gpu(x), gpu(ga), 16, numerics="triton").cpu()
+            assert _same_bits(got, from_np(g[f"y_{nm}_{an}_{dn}"], dt)) == 0, (nm, an)
+    x = from_np(g[f"x_rag_{dn}"], dt)
+    got = ops.qdq_nvfp4_dynamic(gpu(x), gpu(torch.from_numpy(g[f"ga_rag_{dn}"])), 16, numerics="triton").cpu()
+    assert _same_bits(got, from_np(g[f"y_rag_{dn}"], dt)) == 0, "ragged"
+
+
+@pytest.mark.parametrize("dn", list(DTYPES))
+def test_reference_triton_nvfp4_static_bit_exact(ops, dn):
+    g = load_golden("nvfp4_triton_b200.npz")
+    dt = DTYPES[dn]
+    xb = from_np(g[f"x_rand_{dn}"], dt).reshape(-1, 16)
+    bam, gam = torch.from_numpy(g[f"bam_{dn}"]), torch.from_numpy(g[f"gam_{dn}"])
+    for q in (True, False):
+        s = ops.fp4_scales(gpu(bam), gpu(gam), q, 448.0, numerics="triton").cpu()
+        assert _same_bits(s, torch.from_numpy(g[f"sstatic_q{int(q)}_{dn}"])) == 0, ("scales", q)
+        y = ops.qdq_nvfp4_static(gpu(xb), gpu(bam), gpu(gam), q, 448.0, None, numerics="triton").cpu()
+        assert _same_bits(y, from_np(g[f"ystatic_q{int(q)}_{dn}"], dt)) == 0, ("static", q)
+
+
+@pytest.mark.parametrize("dn", list(DTYPES))
+def test_reference_cuda_ext_fp8_int8_bit_exact(ops, dn):
+    g = load_golden("nvfp4_triton_b200.npz")
+    if f"fp8_y_{dn}" not in g:
+        pytest.skip("reference JIT extensions were not captured")
+    dt = DTYPES[dn]
+    x = from_np(g[f"x_rand_{dn}"], dt)
+    am = torch.from_numpy(g[f"fp8_amax_{dn}"]).to(dt)
+    assert _same_bits(ops.qdq_fp8(gpu(x), gpu(am)).cpu(), from_np(g[f"fp8_y_{dn}"], dt)) == 0
+    assert _same_bits(ops.qdq_int(gpu(x), gpu(am), 8, False, False).cpu(), from_np(g[f"int8_y_{dn}"], dt)) == 0
+    amc = torch.from_numpy(g[f"int8c_amax_{dn}"]).to(dt)
+    assert _same_bits(ops.qdq_int(gpu(x), gpu(amc), 8, False, False).cpu(), from_np(g[f"int8c_y_{dn}"], dt)) == 0

@@ -162,3 +162,26 @@ def test_block_scale_underflow_and_zero_block():
     y = ofq.fp4_cast(x)
     assert torch.equal(y[:8], torch.tensor([0.0, -1.0, 1.0, -2.0, 2.0, -4.0, 4.0, 6.0]))
     assert y[9].item() == -6.0  # NaN: all compares false -> 6, sign test false -> negative
+
+
+def test_nvfp4_oracle_vs_reference_triton_on_b200():
+    """The IEEE restatement against outputs of the reference's compiled Triton kernel captured on a B200
+    (tests/golden/nvfp4_triton_b200.npz).  f32/f16: bit-equal.  bf16: the kernel's div.full.f32 moves a
+    few elements per 10^4 across an E2M1 boundary; the product's "triton" numerics
+    mode is what must be bit-equal there (tests/test_gpu_qdq.py)."""
+    import numpy as np  # noqa: F401
+
+    from conftest import DTYPES, from_np, load_golden, n_mismatch
+    from oracle import fake_quant as ofq
+
+    g = load_golden("nvfp4_triton_b200.npz")
+    for dn, dt in DTYPES.items():
+        for nm in ("rand", "adv"):
+            x = from_np(g[f"x_{nm}_{dn}"], dt)
+            for an in ("max", "clip"):
+                ga = torch.from_numpy(g[f"ga_{nm}_{an}_{dn}"])
+                bad = n_mismatch(ofq.nvfp4_dynamic_qdq(x, ga, 16), from_np(g[f"y_{nm}_{an}_{dn}"], dt))
+                if dn == "bf16":
+                    assert bad <= 1e-3 * x.numel(), (dn, nm, an, bad)
+                else:
+                    assert bad == 0, (dn, nm, an, bad)
