@@ -70,6 +70,7 @@ class Clocks:
     def __init__(self, index):
         self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
         self._stop = threading.Event()
+        self._ready = threading.Event()
         self._t = None
 
     def _run(self):
@@ -88,13 +89,16 @@ class Clocks:
                 for n, bit in names.items():
                     if r & bit:
                         self.reasons.add(n)
-                time.sleep(0.02)
+                self._ready.set()
+                time.sleep(0.01)
         except Exception as e:  # noqa: BLE001
             self.reasons.add(f"sampler_error:{type(e).__name__}")
+        self._ready.set()
 
     def __enter__(self):
         self._t = threading.Thread(target=self._run, daemon=True)
         self._t.start()
+        self._ready.wait(timeout=5)
         return self
 
     def __exit__(self, *a):

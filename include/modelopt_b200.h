@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define MO_ABI_VERSION 1
+#define MO_ABI_VERSION 2
 
 typedef enum { MO_F32 = 0, MO_F16 = 1, MO_BF16 = 2 } mo_dtype;
 
@@ -39,9 +39,19 @@ enum {
 #define MO_FLAG_NEGATIVE_IN_UNSIGNED 1u /* tensor_quant_gpu.cu:65-67 CUDA_KERNEL_ASSERT(inputs >= 0) */
 #define MO_FLAG_NEGATIVE_AMAX 2u        /* tensor_quant_gpu.cu:44   CUDA_KERNEL_ASSERT(amax >= 0)   */
 
-/* NVFP4 division numerics. */
-#define MO_DIV_TRITON 0 /* div.full.f32 — what the reference's Triton kernels execute on sm_100a */
-#define MO_DIV_IEEE 1   /* div.rn.f32  — matches the CPU oracle / the torch packer arithmetic    */
+/* Numerics mode: the reference itself computes slightly different scale arithmetic depending on
+ * where it runs, and "bit-exact against the reference" has to say which.
+ *   MO_NUMERICS_GPU  what the reference executes on an sm_100a GPU: div.full.f32 inside its Triton
+ *                    NVFP4 kernels, `tensor / python_scalar` = multiply by the fp32 reciprocal on the
+ *                    host side, true division 448.f / amax in the FP8 CUDA extension
+ *                    (gemm/tensor_quant_gpu_fp8.cu:96-98).  DEFAULT for the product.
+ *   MO_NUMERICS_CPU  what the reference executes on CPU tensors (the oracle): IEEE division everywhere,
+ *                    and Python `448.0 / amax` = reciprocal(amax) * 448 (two roundings; torch
+ *                    Tensor.__rtruediv__) in `_fp8_eager` (tensor_quant.py:46-59).                     */
+#define MO_NUMERICS_GPU 0
+#define MO_NUMERICS_CPU 1
+#define MO_DIV_TRITON MO_NUMERICS_GPU
+#define MO_DIV_IEEE MO_NUMERICS_CPU
 
 int mo_abi_version(void);
 const char* mo_last_error(void);
@@ -70,7 +80,7 @@ int mo_qdq_int(const void* x, void* y, int64_t n, int dtype, const float* amax, 
  * including the host-side torch ops that build scale = 448/amax and inv_scale = 1/scale (:93-98).
  * amax == NULL: plain cast through E4M3 (tensor_quant.py:46-59 with amax=None). */
 int mo_qdq_fp8(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
-               int64_t inner, void* stream);
+               int64_t inner, int numerics, void* stream);
 
 /* Replaces Triton fp4_fake_quant_block (gemm/fp4_kernel_hopper.py:102-170): dynamic NVFP4 over the
  * last dim of a [rows, cols] view; `global_amax` is the calibrated fp32 scalar (device).
@@ -124,7 +134,7 @@ int mo_selftest_exact_div(int q_max, int n_scales, uint64_t seed, uint64_t* mism
  * (pinned or pageable); the call stages chunks through library-owned pinned buffers on two streams
  * so H2D, the kernel and D2H overlap, and returns when y is complete.
  * ---------------------------------------------------------------------------------------------- */
-int mo_qdq_fp8_host(const void* x, void* y, int64_t n, int dtype, float amax);
+int mo_qdq_fp8_host(const void* x, void* y, int64_t n, int dtype, float amax, int numerics);
 int mo_qdq_int_host(const void* x, void* y, int64_t n, int dtype, float amax, int num_bits,
                     int is_unsigned, int narrow_range);
 int mo_qdq_nvfp4_dynamic_host(const void* x, void* y, int64_t rows, int64_t cols, int dtype,

@@ -112,7 +112,7 @@ using namespace mo;
   int rc = g_pipe.init();                                                              \
   if (rc) return rc;
 
-extern "C" int mo_qdq_fp8_host(const void* x, void* y, int64_t n, int dtype, float amax) {
+extern "C" int mo_qdq_fp8_host(const void* x, void* y, int64_t n, int dtype, float amax, int numerics) {
   if (n == 0) return MO_OK;
   MO_HOST_PROLOGUE("mo_qdq_fp8_host")
   if (!y) { set_error("mo_qdq_fp8_host: NULL pointer"); return MO_ERR_NULL; }
@@ -120,7 +120,7 @@ extern "C" int mo_qdq_fp8_host(const void* x, void* y, int64_t n, int dtype, flo
   const float* d_amax = g_pipe.d_scalar;
   return run_chunks(x, y, n, (int64_t)(kChunkBytes / es), es, true,
                     [&](void* di, void* dout, int64_t m, cudaStream_t s) {
-                      return mo_qdq_fp8(di, dout, m, dtype, d_amax, 1, m, s);
+                      return mo_qdq_fp8(di, dout, m, dtype, d_amax, 1, m, numerics, s);
                     });
 }
 

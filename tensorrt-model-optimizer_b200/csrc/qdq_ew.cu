@@ -38,11 +38,12 @@ struct AxisArgs {
 struct Fp8Op {
   AxisArgs ax;
   bool plain;  // amax == NULL: cast only (torch .to(float8_e4m3fn): |x| > 464 or NaN -> NaN)
+  bool eager;  // MO_NUMERICS_CPU: Python `448.0 / amax` == reciprocal(amax) * 448 (tensor_quant.py:52-53)
   float scale, inv;
 
   __device__ __forceinline__ void set(float amax) {
     const float safe = amax <= kEps ? 1.0f : amax;   // tensor_quant_gpu_fp8.cu:94-96
-    scale = __fdiv_rn(448.0f, safe);                  // :97
+    scale = eager ? __fmul_rn(__fdiv_rn(1.0f, safe), 448.0f) : __fdiv_rn(448.0f, safe);  // :97
     inv = __fdiv_rn(1.0f, scale);                     // :98
   }
   __device__ __forceinline__ void init() {
@@ -236,11 +237,12 @@ static int make_axis(AxisArgs& ax, const float* amax, int64_t n, int64_t axis_si
 using namespace mo;
 
 extern "C" int mo_qdq_fp8(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
-                          int64_t inner, void* stream) {
+                          int64_t inner, int numerics, void* stream) {
   if (n == 0) return MO_OK;
   if (!x || !y) { set_error("mo_qdq_fp8: x/y is NULL"); return MO_ERR_NULL; }
   Fp8Op op;
   op.plain = amax == nullptr;
+  op.eager = numerics == MO_NUMERICS_CPU;
   if (op.plain) { axis_size = 1; inner = n; }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   int rc;

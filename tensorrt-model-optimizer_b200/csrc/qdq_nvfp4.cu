@@ -231,7 +231,8 @@ __global__ void __launch_bounds__(kThreads) fp4_scales_kernel(const float* __res
     float sa = __fmul_rn(ga, k);
     sa = kIeee ? __fdiv_rn(sa, 6.0f) : __fmul_rn(sa, 1.0f / 6.0f);
     const float safe = sa <= kEps ? 1.0f : sa;
-    sc = __fdiv_rn(448.0f, safe);
+    // scaled_e4m3_impl: CUDA extension on the GPU (true division), `_fp8_eager` on CPU (reciprocal * 448)
+    sc = kIeee ? __fmul_rn(__fdiv_rn(1.0f, safe), 448.0f) : __fdiv_rn(448.0f, safe);
     inv = __fdiv_rn(1.0f, sc);
   }
   for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {

@@ -12,9 +12,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libmodelopt_b200.so")
 
 MO_F32, MO_F16, MO_BF16 = 0, 1, 2
-MO_DIV_TRITON, MO_DIV_IEEE = 0, 1
+MO_NUMERICS_GPU, MO_NUMERICS_CPU = 0, 1
+MO_DIV_TRITON, MO_DIV_IEEE = MO_NUMERICS_GPU, MO_NUMERICS_CPU
 MO_FLAG_NEGATIVE_IN_UNSIGNED, MO_FLAG_NEGATIVE_AMAX = 1, 2
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 
@@ -23,7 +24,7 @@ SIGNATURES = {
     "mo_abi_version": [],
     "mo_device_info": [C.c_char_p, _i, C.POINTER(_i), C.POINTER(_i)],
     "mo_qdq_int": [_p, _p, _i64, _i, _p, _i64, _i64, _i, _i, _i, _p, _p],
-    "mo_qdq_fp8": [_p, _p, _i64, _i, _p, _i64, _i64, _p],
+    "mo_qdq_fp8": [_p, _p, _i64, _i, _p, _i64, _i64, _i, _p],
     "mo_qdq_nvfp4_dynamic": [_p, _p, _i64, _i64, _i, _p, _i, _i, _p],
     "mo_qdq_nvfp4_static": [_p, _p, _i64, _i, _i, _i, _p, _i, _p],
     "mo_fp4_scales": [_p, _p, _i64, _p, _i, _f, _i, _p, _p],
@@ -31,7 +32,7 @@ SIGNATURES = {
     "mo_amax": [_p, _i64, _i64, _i64, _i, _p, _p],
     "mo_selftest_e2m1": [C.POINTER(C.c_uint64)],
     "mo_selftest_exact_div": [_i, _i, C.c_uint64, C.POINTER(C.c_uint64)],
-    "mo_qdq_fp8_host": [_p, _p, _i64, _i, _f],
+    "mo_qdq_fp8_host": [_p, _p, _i64, _i, _f, _i],
     "mo_qdq_int_host": [_p, _p, _i64, _i, _f, _i, _i, _i],
     "mo_qdq_nvfp4_dynamic_host": [_p, _p, _i64, _i64, _i, _f, _i, _i],
     "mo_amax_host": [_p, _i64, _i, C.POINTER(_f)],

@@ -22,16 +22,20 @@ def _launched(rc, what, n=1):
     LAUNCHES[0] += n
 
 
+_CPU_NAMES = ("ieee", "cpu")
+
+
 def default_numerics() -> int:
-    """NVFP4 numerics mode: 'triton' (what the reference runs on a GPU, default) or 'ieee'."""
-    return MO_DIV_IEEE if os.environ.get("MODELOPT_B200_NUMERICS", "triton").lower() == "ieee" else MO_DIV_TRITON
+    """Numerics mode (include/modelopt_b200.h MO_NUMERICS_*): 'gpu' / 'triton' = what the reference executes
+    on a GPU (default), 'cpu' / 'ieee' = what it executes on CPU tensors (the oracle)."""
+    return MO_DIV_IEEE if os.environ.get("MODELOPT_B200_NUMERICS", "gpu").lower() in _CPU_NAMES else MO_DIV_TRITON
 
 
 def _mode(numerics) -> int:
     if numerics is None:
         return default_numerics()
     if isinstance(numerics, str):
-        return MO_DIV_IEEE if numerics.lower() == "ieee" else MO_DIV_TRITON
+        return MO_DIV_IEEE if numerics.lower() in _CPU_NAMES else MO_DIV_TRITON
     return int(numerics)
 
 
@@ -120,10 +124,10 @@ def qdq_int(x, amax, num_bits=8, unsigned=False, narrow_range=True, out=None, st
     return y
 
 
-def qdq_fp8(x, amax=None, out=None):
+def qdq_fp8(x, amax=None, out=None, numerics=None):
     _cuda(x, "qdq_fp8")
     if x.dtype == torch.float64:
-        return _via_f32(qdq_fp8, x, amax)
+        return _via_f32(qdq_fp8, x, amax, None, numerics)
     x = x.contiguous()
     y = torch.empty_like(x) if out is None else out
     if amax is None:
@@ -134,7 +138,7 @@ def qdq_fp8(x, amax=None, out=None):
         ap = am.data_ptr()
     with _dev(x):
         _launched(_lib.load().mo_qdq_fp8(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), ap, axis_size, inner,
-                                     _stream(x)), "mo_qdq_fp8")
+                                     _mode(numerics), _stream(x)), "mo_qdq_fp8")
     return y
 
 
@@ -307,11 +311,11 @@ def amax_host(x: torch.Tensor) -> float:
     return out.value
 
 
-def qdq_fp8_host(x: torch.Tensor, amax: float, out: torch.Tensor | None = None) -> torch.Tensor:
+def qdq_fp8_host(x: torch.Tensor, amax: float, out: torch.Tensor | None = None, numerics=None) -> torch.Tensor:
     _host(x, "qdq_fp8_host")
     y = torch.empty_like(x) if out is None else out
-    _launched(_lib.load().mo_qdq_fp8_host(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), float(amax)),
-              "mo_qdq_fp8_host", n=_chunks(x))
+    _launched(_lib.load().mo_qdq_fp8_host(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), float(amax),
+                                          _mode(numerics)), "mo_qdq_fp8_host", n=_chunks(x))
     return y
 
 

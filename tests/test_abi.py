@@ -37,7 +37,7 @@ def test_argument_errors_without_gpu():
     assert b"num_bits" in lib.mo_last_error()
     assert lib.mo_qdq_nvfp4_dynamic(p, p, 1, 16, 2, p, 8, 0, None) == -3  # block not in {16,32,64}
     assert lib.mo_amax(p, 1, 0, 16, 2, p, None) == -2  # MO_ERR_SHAPE
-    assert lib.mo_qdq_fp8(p, p, 0, 2, p, 1, 0, None) == 0  # empty tensor is a no-op
+    assert lib.mo_qdq_fp8(p, p, 0, 2, p, 1, 0, 0, None) == 0  # empty tensor is a no-op
 
 
 def test_cpu_tensor_is_rejected_loudly():
