@@ -121,6 +121,39 @@ int mo_amax(const void* x, int64_t outer, int64_t axis_size, int64_t inner, int 
             uint32_t* amax_bits, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Histogram calibration (rows a9, a10): replaces HistogramCalibrator.collect and the three amax
+ * searches (calib/histogram.py:77-130, :210-343).
+ * ---------------------------------------------------------------------------------------------- */
+/* One read of x: bins |x| with torch.histc's rule (bin = (int)(v * nbins / range_max), v in
+ * [0, range_max], last bin closed; range_max == 0 -> range [-1, 1]) into `counts` (device uint64[nbins],
+ * ADDED to: exact integer counts, where the reference's fp32 histc saturates at 2^24 per bin), and
+ * merges max|x| into `amax_bits` (optional, as mo_amax).  range_max is a DEVICE fp32 scalar.
+ * skip_zeros: histogram.py:107-108. */
+int mo_hist(const void* x, int64_t n, int dtype, const float* range_max, int64_t nbins, uint64_t* counts,
+            uint32_t* amax_bits, int skip_zeros, void* stream);
+
+/* _compute_amax_percentile (histogram.py:328-343): *idx_out (device) = searchsorted(cumsum(hist/total),
+ * percentile/100) in fp64, numpy's summation order; the amax is edges[idx]. */
+int mo_hist_percentile(const uint64_t* counts, int64_t nbins, double percentile, int32_t* idx_out,
+                       void* stream);
+
+/* _compute_amax_mse (histogram.py:285-325): *idx_out = argmin over candidates i = start_bin + k*stride of
+ * mean((fq(centres; amax = centre_i) - centres)^2 * counts); the amax is centre[start_bin + idx*stride].
+ * as_written = 1 reproduces the reference's mis-slotted call (bias <- num_bits, num_bits <- unsigned,
+ * :308); 0 evaluates the intended INT-N (fp8 = 0) or E4M3 (fp8 = 1) fake-quant.
+ * edges: device fp32[nbins + 1]; loss_scratch: device double[number of candidates]. */
+int mo_hist_mse(const uint64_t* counts, const float* edges, int64_t nbins, int num_bits, int is_unsigned,
+                int fp8, int as_written, int stride, int start_bin, double* loss_scratch, int32_t* idx_out,
+                void* stream);
+
+/* _compute_amax_entropy (histogram.py:210-282): TensorRT-style KL search in fp64; *idx_out = index of the
+ * LAST minimum over candidates i = start_bin, start_bin + stride, ..., <= nbins; the amax is
+ * edges[start_bin + idx*stride].  scratch: device buffer of mo_hist_entropy_scratch_bytes(). */
+int64_t mo_hist_entropy_scratch_bytes(int64_t nbins, int stride, int start_bin);
+int mo_hist_entropy(const uint64_t* counts, int64_t nbins, int num_bits, int is_unsigned, int stride,
+                    int start_bin, void* scratch, int32_t* idx_out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.
  * ---------------------------------------------------------------------------------------------- */

@@ -171,8 +171,92 @@ def gen_nvfp4_pack():
     print("nvfp4_pack_cpu.npz", len(g), "arrays")
 
 
+def _tiny_model(dt=torch.float32):
+    from torch import nn
+
+    torch.manual_seed(77)
+    m = nn.Sequential(nn.Linear(256, 512), nn.ReLU(), nn.Linear(512, 256, bias=False)).to(dt)
+    return m
+
+
+def gen_quantize():
+    """mtq.quantize end to end on CPU with the reference: calibrated amax of every quantizer and model outputs."""
+    import copy
+
+    import modelopt.torch.quantization as mtq
+
+    g = {}
+    gen = torch.Generator().manual_seed(5)
+    batches = [torch.randn(8, 16, 256, generator=gen) * (1 + i) for i in range(3)]
+    test = torch.randn(4, 16, 256, generator=gen) * 2
+    base = _tiny_model()
+    for k, v in base.state_dict().items():
+        g[f"w_{k}"] = to_np(v)
+    for i, b in enumerate(batches):
+        g[f"batch{i}"] = to_np(b)
+    g["test"] = to_np(test)
+    for name in ("INT8_DEFAULT_CFG", "FP8_DEFAULT_CFG", "INT4_BLOCKWISE_WEIGHT_ONLY_CFG", "NVFP4_DEFAULT_CFG",
+                 "INT8_SMOOTHQUANT_CFG", "INT4_AWQ_CFG"):
+        m = copy.deepcopy(base)
+
+        def loop(model):
+            for b in batches:
+                model(b)
+
+        m = mtq.quantize(m, copy.deepcopy(getattr(mtq, name)), loop)
+        for n, mod in m.named_modules():
+            if isinstance(mod, mtq.nn.TensorQuantizer):
+                g[f"{name}|{n}|enabled"] = np.asarray(mod.is_enabled)
+                for buf in ("_amax", "_pre_quant_scale"):
+                    if hasattr(mod, buf):
+                        g[f"{name}|{n}|{buf}"] = to_np(getattr(mod, buf).float())
+        for k, v in m.state_dict().items():
+            if "quantizer" not in k and not torch.equal(v, base.state_dict()[k]):
+                g[f"{name}|weight_after|{k}"] = to_np(v)
+        if name != "NVFP4_DEFAULT_CFG":  # NVFP4 fake-quant has no CPU path in the reference
+            with torch.no_grad():
+                g[f"{name}|out"] = to_np(m(test))
+    np.savez_compressed(os.path.join(OUT, "quantize_cpu.npz"), **g)
+    print("quantize_cpu.npz", len(g), "arrays")
+
+
+def gen_hist():
+    from modelopt.torch.quantization.calib import HistogramCalibrator
+
+    g = {}
+    torch.manual_seed(31)
+    cases = {
+        "grow": [torch.randn(32, 512) * (1.0 + 0.25 * i) for i in range(3)],       # range grows every batch
+        "same": [torch.randn(16, 1024).clamp(-3, 3) for _ in range(2)] + [torch.randn(16, 1024) * 0.5],
+        "pos": [torch.rand(24, 256) * 4.0, torch.rand(24, 256) * 5.0],              # non-negative (no abs path)
+    }
+    cases["same"][0][0, 0] = 3.0
+    for cn, xs in cases.items():
+        for dn, dt in (("f32", torch.float32), ("bf16", torch.bfloat16)):
+            xs_d = [x.to(dt) for x in xs]
+            for bits, uns in ((8, False), (4, False), (8, True)):
+                if uns and cn != "pos":
+                    continue
+                c = HistogramCalibrator(bits, None, uns)
+                for i, x in enumerate(xs_d):
+                    c.collect(x)
+                    g[f"{cn}_{dn}_x{i}"] = to_np(x)
+                    g[f"{cn}_{dn}_hist{i}"] = to_np(c._calib_hist.clone())
+                    g[f"{cn}_{dn}_edges{i}"] = to_np(c._calib_bin_edges.clone())
+                k = f"{cn}_{dn}_b{bits}_u{int(uns)}"
+                for pct in (99.0, 99.9, 99.99, 100.0):
+                    g[f"{k}_pct{pct}"] = to_np(c.compute_amax("percentile", percentile=pct))
+                g[f"{k}_mse"] = to_np(c.compute_amax("mse"))
+                g[f"{k}_mse_s4"] = to_np(c.compute_amax("mse", stride=4, start_bin=256))
+                # entropy LAST: it writes hist[0] = hist[1] into a copy (.int() copies), the calibrator is unchanged
+                g[f"{k}_entropy"] = to_np(c.compute_amax("entropy"))
+                g[f"{k}_entropy_s3"] = to_np(c.compute_amax("entropy", stride=3, start_bin=200))
+    np.savez_compressed(os.path.join(OUT, "hist_cpu.npz"), **g)
+    print("hist_cpu.npz", len(g), "arrays")
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack"]
+    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack", "hist", "quantize"]
     for w in which:
         globals()["gen_" + w]()

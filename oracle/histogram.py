@@ -15,8 +15,6 @@ Parity: pinned against the real reference by tests/golden/hist_cpu.npz (oracle/g
 
 from __future__ import annotations
 
-from collections import Counter
-
 import numpy as np
 import torch
 
@@ -48,7 +46,7 @@ class HistogramCalibrator:
             if x_max > self._calib_bin_edges[-1]:
                 width = self._calib_bin_edges[1] - self._calib_bin_edges[0]
                 self._num_bins = int((x_max / width).ceil().item())
-                self._calib_bin_edges = torch.arange(0, x_max + width, width)
+                self._calib_bin_edges = torch.arange(0, x_max + width, width, device=x.device)
             hist = torch.histc(x, bins=self._num_bins, min=0, max=self._calib_bin_edges[-1])
             hist[: self._calib_hist.numel()] += self._calib_hist
             self._calib_hist = hist
@@ -81,42 +79,39 @@ def _entropy(pk: np.ndarray, qk: np.ndarray) -> float:
 
 
 def compute_amax_entropy(calib_hist, calib_bin_edges, num_bits, unsigned, stride=1, start_bin=128):
-    """histogram.py:210-282.  Quirks kept: ``bins[0] = bins[1]`` mutates the caller's array (numpy slice is a
-    view), ``_normalize_distr`` is a no-op, the LAST argmin wins."""
+    """histogram.py:210-282, vectorised per candidate.  For a candidate of ``i`` source bins the first ``i`` bins
+    are merged into ``nbins = 2^(bits-1+unsigned)`` equal-width groups; every NON-EMPTY source bin of a group gets
+    the group's mean over its non-empty bins; KL(reference || that) with the clipped tail folded into bin i-1.
+    Quirks kept: ``hist[0] = hist[1]`` is written into the caller's array (``calib_hist[:]`` is a numpy view), the
+    two distributions reach ``entropy`` un-normalised (the reference's normaliser discards its result; scipy
+    normalises internally) and ties go to the LAST minimum."""
     if calib_bin_edges is None and calib_hist is None:
         return None
-    bins = calib_hist[:]
-    bins[0] = bins[1]
-    total_data = np.sum(bins)
-    divergences = []
+    try:
+        from scipy.stats import entropy
+    except ImportError:  # pragma: no cover
+        entropy = _entropy
+    hist = calib_hist
+    hist[0] = hist[1]
+    total = np.sum(hist)
     nbins = 1 << (num_bits - 1 + int(unsigned))
-    new_density_counts = np.zeros(nbins, dtype=np.float64)
-    for i in range(start_bin, len(bins) + 1, stride):
-        new_density_counts.fill(0)
-        space = np.linspace(0, i, num=nbins + 1)
-        digitized_space = np.digitize(range(i), space) - 1
-        digitized_space[bins[:i] == 0] = -1
-        for idx, digitized in enumerate(digitized_space):
-            if digitized != -1:
-                new_density_counts[digitized] += bins[idx]
-        counter = Counter(digitized_space)
-        for key, val in counter.items():
-            if key != -1:
-                new_density_counts[key] = new_density_counts[key] / val
-        new_density = np.zeros(i, dtype=np.float64)
-        for idx, digitized in enumerate(digitized_space):
-            if digitized != -1:
-                new_density[idx] = new_density_counts[digitized]
-        total_counts_new = np.sum(new_density) + np.sum(bins[i:])
-        reference_density = np.array(bins[: len(digitized_space)])
-        reference_density[-1] += np.sum(bins[i:])
-        total_counts_old = np.sum(reference_density)
-        if round(total_counts_new) != total_data or round(total_counts_old) != total_data:
+    candidates = list(range(start_bin, len(hist) + 1, stride))
+    kl = np.empty(len(candidates), dtype=np.float64)
+    for n, i in enumerate(candidates):
+        head = hist[:i]
+        group = np.digitize(np.arange(i), np.linspace(0, i, num=nbins + 1)) - 1
+        live = head != 0
+        sums = np.bincount(group[live], weights=head[live].astype(np.float64), minlength=nbins)
+        cnts = np.bincount(group[live], minlength=nbins)
+        mean = np.divide(sums, cnts, out=np.zeros(nbins, dtype=np.float64), where=cnts > 0)
+        q = np.where(live, mean[group], 0.0)
+        p = np.array(head)
+        p[-1] += np.sum(hist[i:])
+        if round(np.sum(q) + np.sum(hist[i:])) != total or round(np.sum(p)) != total:
             raise RuntimeError("Count mismatch!")
-        divergences.append(_entropy(reference_density, new_density))
-    divergences = np.array(divergences)
-    last_argmin = len(divergences) - 1 - np.argmin(divergences[::-1])
-    return torch.tensor(calib_bin_edges[last_argmin * stride + start_bin].item())
+        kl[n] = entropy(p, q)
+    best = len(kl) - 1 - int(np.argmin(kl[::-1]))
+    return torch.tensor(calib_bin_edges[best * stride + start_bin].item())
 
 
 def _tensor_quant_legacy(inputs, amax, num_bits, unsigned, narrow_range=True):

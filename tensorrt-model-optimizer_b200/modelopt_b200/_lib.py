@@ -30,6 +30,11 @@ SIGNATURES = {
     "mo_fp4_scales": [_p, _p, _i64, _p, _i, _f, _i, _p, _p],
     "mo_fp4_cast": [_p, _p, _i64, _i, _i, _p],
     "mo_amax": [_p, _i64, _i64, _i64, _i, _p, _p],
+    "mo_hist": [_p, _i64, _i, _p, _i64, _p, _p, _i, _p],
+    "mo_hist_percentile": [_p, _i64, C.c_double, _p, _p],
+    "mo_hist_mse": [_p, _p, _i64, _i, _i, _i, _i, _i, _i, _p, _p, _p],
+    "mo_hist_entropy_scratch_bytes": [_i64, _i, _i],
+    "mo_hist_entropy": [_p, _i64, _i, _i, _i, _i, _p, _p, _p],
     "mo_selftest_e2m1": [C.POINTER(C.c_uint64)],
     "mo_selftest_exact_div": [_i, _i, C.c_uint64, C.POINTER(C.c_uint64)],
     "mo_qdq_fp8_host": [_p, _p, _i64, _i, _f, _i],
@@ -59,7 +64,7 @@ def load() -> C.CDLL:
     for name, argtypes in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.argtypes = argtypes
-        fn.restype = _i
+        fn.restype = _i64 if name.endswith("_bytes") else _i
     lib.mo_last_error.argtypes = []
     lib.mo_last_error.restype = C.c_char_p
     if lib.mo_abi_version() != ABI_VERSION:

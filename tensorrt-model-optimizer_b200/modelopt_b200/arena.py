@@ -76,3 +76,27 @@ class AmaxArena:
         bad = torch.stack([torch.isnan(a).any(), torch.isinf(a).any()]).tolist()
         assert not bad[0], "detected nan values in amax"
         assert not bad[1], "detected inf values in amax"
+
+
+class AmaxArenaPool:
+    """One arena per device, created on first use (calibrators learn their device at the first collect)."""
+
+    def __init__(self):
+        self._arenas: dict[torch.device, AmaxArena] = {}
+
+    def get(self, device) -> AmaxArena:
+        device = torch.device(device)
+        if device not in self._arenas:
+            self._arenas[device] = AmaxArena(device)
+        return self._arenas[device]
+
+    def arenas(self):
+        return list(self._arenas.values())
+
+    def sync(self, group=None):
+        for a in self._arenas.values():
+            a.sync(group)
+
+    def check(self):
+        for a in self._arenas.values():
+            a.check()

@@ -1,0 +1,5 @@
+"""Calibrators (mirror of modelopt.torch.quantization.calib)."""
+
+from .calibrator import *  # noqa: F401,F403
+from .histogram import *  # noqa: F401,F403
+from .max import *  # noqa: F401,F403

@@ -1,0 +1,135 @@
+"""Model conversion: insert quantizers, apply a quant_cfg (interface of modelopt/torch/quantization/conversion.py:
+``replace_quant_module`` :214, ``set_quantizer_by_cfg`` :245, ``set_quantizer_attributes_full/partial`` :367-500,
+``quantizer_state`` :205)."""
+
+from __future__ import annotations
+
+import fnmatch
+import re
+from collections.abc import Callable
+from typing import Any
+
+from torch import nn
+
+from .config import QuantizerAttributeConfig, normalize_quant_cfg_list
+from .nn.quant_module import QuantModuleRegistry
+from .nn.tensor_quantizer import SequentialQuantizer, TensorQuantizer
+from .utils import is_quantized
+
+__all__ = ["replace_quant_module", "set_quantizer_by_cfg", "set_quantizer_attribute", "set_quantizer_attributes_full",
+           "set_quantizer_attributes_partial", "quantizer_state", "restore_quantizer_state"]
+
+_EXPERT_LIST_RE = re.compile(r"(weight_quantizers?|input_quantizers?)\.\d+(?=$|\.)")
+
+
+def replace_quant_module(model: nn.Module, registry=QuantModuleRegistry):
+    """Recursively swap every registered module type for its quantized version (in place)."""
+    assert not is_quantized(model), "Model must not be quantized!"
+    if type(model) in registry:
+        model = registry.convert(model)
+
+    def walk(parent):
+        for name, child in parent.named_children():
+            if type(child) in registry:
+                setattr(parent, name, registry.convert(child))
+            walk(getattr(parent, name))
+
+    walk(model)
+    n = sum(isinstance(m, TensorQuantizer) for m in model.modules())
+    print(f"Inserted {n} quantizers")
+    return model
+
+
+def _match(pattern: str | Callable, name: str, module, parent_class, model) -> bool:
+    if not isinstance(module, (TensorQuantizer, SequentialQuantizer)):
+        return False
+    if isinstance(pattern, str):
+        norm = _EXPERT_LIST_RE.sub(lambda m: m.group(1).removesuffix("s"), name)
+        if not (fnmatch.fnmatch(name, pattern) or (norm != name and fnmatch.fnmatch(norm, pattern))):
+            return False
+    elif callable(pattern):
+        if not pattern(name):
+            return False
+    else:
+        raise NotImplementedError(f"Unsupported type {type(pattern)}")
+    if parent_class is None:
+        return True
+    return isinstance(model.get_submodule(".".join(name.split(".")[:-1])), parent_class)
+
+
+def set_quantizer_attributes_full(model, pattern, attributes, parent_class=None):
+    """Replace ALL attributes of the matched quantizers (unspecified fields revert to their defaults); a list of
+    configs turns the quantizer into a SequentialQuantizer."""
+    if not isinstance(attributes, (QuantizerAttributeConfig, list)):
+        raise ValueError(f"Invalid type for attributes: {type(attributes)}")
+    for name, module in list(model.named_modules()):
+        if not _match(pattern, name, module, parent_class, model):
+            continue
+        if isinstance(attributes, list):
+            if not isinstance(module, SequentialQuantizer) or len(module) != len(attributes):
+                parent = model.get_submodule(".".join(name.split(".")[:-1]))
+                module = SequentialQuantizer(*(TensorQuantizer() for _ in attributes))
+                setattr(parent, name.split(".")[-1], module)
+            module.set_from_attribute_config(attributes)
+        else:
+            if isinstance(module, SequentialQuantizer):
+                parent = model.get_submodule(".".join(name.split(".")[:-1]))
+                module = TensorQuantizer()
+                setattr(parent, name.split(".")[-1], module)
+            module.set_from_attribute_config(attributes)
+
+
+def set_quantizer_attributes_partial(model, pattern, attributes: dict[str, Any], parent_class=None):
+    """Update only the given attributes of the matched quantizers."""
+    for name, module in model.named_modules():
+        if _match(pattern, name, module, parent_class, model):
+            targets = module if isinstance(module, SequentialQuantizer) else [module]
+            for q in targets:
+                q.set_from_attribute_config(attributes)
+
+
+def set_quantizer_attribute(model, pattern, attribute, parent_class=None):
+    """Legacy name: a dict updates partially, a QuantizerAttributeConfig / list replaces fully."""
+    if isinstance(attribute, dict):
+        set_quantizer_attributes_partial(model, pattern, attribute, parent_class)
+    else:
+        set_quantizer_attributes_full(model, pattern, attribute, parent_class)
+
+
+def set_quantizer_by_cfg(model: nn.Module, quant_cfg):
+    """Apply an ordered quant_cfg list: later entries override earlier ones; an entry with ``cfg`` is a complete
+    replacement, an entry with only ``enable`` toggles."""
+    for entry in normalize_quant_cfg_list(quant_cfg):
+        name, cfg, enable = entry["quantizer_name"], entry["cfg"], entry["enable"]
+        pc = entry.get("parent_class")
+        if pc:
+            try:
+                parent_class = QuantModuleRegistry[pc]
+            except KeyError:
+                raise ValueError(f"parent_class {pc!r} not found in QuantModuleRegistry.") from None
+        else:
+            parent_class = None
+        if cfg is None:
+            set_quantizer_attributes_partial(model, name, {"enable": enable}, parent_class)
+        elif isinstance(cfg, QuantizerAttributeConfig):
+            set_quantizer_attributes_full(model, name, cfg.model_copy(update={"enable": enable}), parent_class)
+        elif isinstance(cfg, dict):
+            set_quantizer_attributes_full(model, name, QuantizerAttributeConfig(**cfg, enable=enable), parent_class)
+        else:
+            attrs = [c.model_copy(update={"enable": enable}) if isinstance(c, QuantizerAttributeConfig)
+                     else QuantizerAttributeConfig(**c, enable=enable) for c in cfg]
+            set_quantizer_attributes_full(model, name, attrs, parent_class)
+
+
+def quantizer_state(model: nn.Module) -> dict[str, Any]:
+    """name -> TensorQuantizer.get_modelopt_state() (what a checkpoint needs beside the state_dict)."""
+    return {n: m.get_modelopt_state() for n, m in model.named_modules()
+            if isinstance(m, (TensorQuantizer, SequentialQuantizer))}
+
+
+def restore_quantizer_state(model: nn.Module, state: dict[str, Any]):
+    """Inverse of ``quantizer_state`` on a model that went through ``replace_quant_module``."""
+    for n, m in model.named_modules():
+        if isinstance(m, TensorQuantizer) and n in state:
+            m.set_from_modelopt_state(state[n])
+    return model

@@ -1,0 +1,272 @@
+"""Quantized wrappers of torch modules (interface of modelopt/torch/quantization/nn/modules/quant_module.py:41-300,
+quant_linear.py:38-53, quant_conv.py, plugins/huggingface.py:559-575).
+
+A module is converted IN PLACE: its class is swapped for a generated subclass ``Quant<Orig>`` that adds
+``input_quantizer`` / ``output_quantizer`` (and ``weight_quantizer`` for linear / conv) and quantizes in ``forward``:
+
+    out = output_quantizer(orig_forward(input_quantizer(x)))      with  self.weight -> weight_quantizer(weight)
+
+Parameters, buffers, hooks and the state_dict layout of the original module are untouched, so checkpoints keep
+loading.  One B200-specific behaviour: while a weight quantizer is only *collecting* with a ``MaxCalibrator`` the
+result cannot change between forwards unless the weight does, so the re-collection the reference does on every
+forward (a 2 x 14 GB read per micro-batch for Llama-3-8B) is skipped when the weight's
+(data_ptr, version) is unchanged — max is idempotent, outputs are identical.
+"""
+
+from __future__ import annotations
+
+import contextlib
+import warnings
+from typing import Any
+
+import torch
+from torch import nn
+
+from ..calib import MaxCalibrator
+from ..config import QuantizerAttributeConfig
+from .tensor_quantizer import SequentialQuantizer, TensorQuantizer
+
+__all__ = ["QuantModule", "QuantInputBase", "QuantLinearConvBase", "QuantModuleRegistry", "ParallelState"]
+
+QUANT_DESC_8BIT_PER_TENSOR = QuantizerAttributeConfig(num_bits=8)
+QUANT_DESC_8BIT_LINEAR_WEIGHT_PER_ROW = QuantizerAttributeConfig(num_bits=8, axis=(0,))
+
+
+class ParallelState:
+    """Process groups a quantized module synchronises calibration statistics over
+    (modelopt/torch/utils/distributed.py:441-480).  ``None`` = the default (world) group; ``-1`` = no group."""
+
+    def __init__(self, data_parallel_group=None, tensor_parallel_group=-1, expert_model_parallel_group=-1):
+        self.data_parallel_group = data_parallel_group
+        self.tensor_parallel_group = tensor_parallel_group
+        self.expert_model_parallel_group = expert_model_parallel_group
+
+    def __repr__(self):
+        return (f"ParallelState(dp={self.data_parallel_group}, tp={self.tensor_parallel_group}, "
+                f"ep={self.expert_model_parallel_group})")
+
+
+class QuantModule(nn.Module):
+    """Base of every generated quantized class."""
+
+    _parallel_state: ParallelState
+    _original_cls: type
+
+    def _setup(self):
+        raise NotImplementedError
+
+    @property
+    def parallel_state(self):
+        return getattr(self, "_parallel_state", None)
+
+    @parallel_state.setter
+    def parallel_state(self, value):
+        assert isinstance(value, ParallelState), "parallel_state must be a ParallelState object!"
+        self._parallel_state = value
+
+    def iter_weights_for_calibration(self):
+        """Yield ``(weight, weight_quantizer)`` pairs for weight-only calibration."""
+        if hasattr(self, "weight_quantizer") and getattr(self, "weight", None) is not None:
+            yield self._parameters["weight"], self.weight_quantizer
+
+    def fold_weight(self, keep_attrs: bool = False):
+        """quant_module.py:160-186: replace the weight by its fake-quantized value (computed in fp32) and switch the
+        weight quantizer off."""
+        for weight, q in self.iter_weights_for_calibration():
+            if isinstance(q, (TensorQuantizer, SequentialQuantizer)) and getattr(q, "fake_quant", True) \
+                    and getattr(q, "is_enabled", True):
+                with torch.no_grad():
+                    weight.data.copy_(q(weight.float().contiguous()).to(weight.dtype))
+                q.disable()
+                if not keep_attrs:
+                    for name in ("_pre_quant_scale", "_amax"):
+                        if hasattr(q, name):
+                            delattr(q, name)
+
+    def modelopt_post_restore(self, prefix: str = ""):
+        ref = next((p for n, p in self.state_dict().items() if "_quantizer" not in n), None)
+        if ref is None:
+            warnings.warn(f"Could not identify the device for TensorQuantizer states of {prefix}.")
+            return
+        for m in self.modules():
+            if isinstance(m, TensorQuantizer):
+                m.to(ref.device)
+
+
+class QuantInputBase(QuantModule):
+    """Modules whose input (and optionally output) is quantized."""
+
+    default_quant_desc_input = QUANT_DESC_8BIT_PER_TENSOR
+    default_quant_desc_output = QUANT_DESC_8BIT_PER_TENSOR
+
+    def _setup(self):
+        self.input_quantizer = TensorQuantizer(self.default_quant_desc_input)
+        self.output_quantizer = TensorQuantizer(self.default_quant_desc_output)
+        self.output_quantizer.disable()
+
+    def forward(self, input, *args, **kwargs):
+        input = self.input_quantizer(input)
+        output = self._original_cls.forward(self, input, *args, **kwargs)
+        if isinstance(output, tuple):
+            return (self.output_quantizer(output[0]), *output[1:])
+        return self.output_quantizer(output)
+
+
+def _weight_get(self):
+    w = self._parameters["weight"] if "weight" in self._parameters else self._buffers.get("weight")
+    if w is None or not self.__dict__.get("_enable_weight_quantization", False):
+        return w
+    q = self.weight_quantizer
+    if (isinstance(q, TensorQuantizer) and q._if_calib and not q._if_quant and not q._disabled
+            and isinstance(q._calibrator, MaxCalibrator) and q.pre_quant_scale is None):
+        key = (w.data_ptr(), w._version, tuple(w.shape))
+        if self.__dict__.get("_weight_collect_key") == key and q._calibrator._shape is not None:
+            return w  # already folded into the running amax; max is idempotent
+        self.__dict__["_weight_collect_key"] = key
+    return q(w)
+
+
+def _weight_set(self, value):
+    # nn.Module.__setattr__ routes Parameters to register_parameter before a class property is consulted; this is
+    # only reached for plain tensors / None
+    if value is None or isinstance(value, nn.Parameter):
+        self.register_parameter("weight", value)
+    else:
+        self._parameters["weight"] = value
+
+
+class QuantLinearConvBase(QuantInputBase):
+    """Linear / conv modules: input and weight are quantized."""
+
+    default_quant_desc_weight = QUANT_DESC_8BIT_PER_TENSOR
+    # generated subclasses get:  weight = property(_weight_get, _weight_set)
+
+    def _setup(self):
+        super()._setup()
+        self.weight_quantizer = TensorQuantizer(self.default_quant_desc_weight)
+        self.__dict__["_enable_weight_quantization"] = False
+
+    @contextlib.contextmanager
+    def quantize_weight(self):
+        """Context in which ``self.weight`` reads as the quantized weight."""
+        self.__dict__["_enable_weight_quantization"] = True
+        try:
+            yield
+        finally:
+            self.__dict__["_enable_weight_quantization"] = False
+
+    def forward(self, input, *args, **kwargs):
+        with self.quantize_weight():
+            return super().forward(input, *args, **kwargs)
+
+    @staticmethod
+    def quantized_linear_fn(package, func_name, self, input, weight, *args, **kwargs):
+        """quant_linear.py:44-53."""
+        out = getattr(package, func_name)(self.input_quantizer(input), self.weight_quantizer(weight), *args, **kwargs)
+        return self.output_quantizer(out)
+
+
+class _QuantLinear(QuantLinearConvBase):
+    default_quant_desc_weight = QUANT_DESC_8BIT_LINEAR_WEIGHT_PER_ROW
+
+
+class _QuantConv(QuantLinearConvBase):
+    default_quant_desc_weight = QUANT_DESC_8BIT_LINEAR_WEIGHT_PER_ROW
+
+
+class _Registry:
+    """original class -> quantized base (QuantModuleRegistry of the reference: ``in``, ``[name]``, ``convert``)."""
+
+    def __init__(self):
+        self._by_cls: dict[type, tuple[str, type, Any]] = {}
+        self._generated: dict[type, type] = {}
+
+    def register(self, mapping: dict[type, str], pre_convert=None):
+        def deco(base):
+            for cls, name in mapping.items():
+                self._by_cls[cls] = (name, base, pre_convert)
+            return base
+        return deco
+
+    def unregister(self, cls):
+        self._by_cls.pop(cls, None)
+        self._generated.pop(cls, None)
+
+    def __contains__(self, cls):
+        return cls in self._by_cls
+
+    def __getitem__(self, name: str):
+        """Generated quantized class registered under ``name`` (e.g. "nn.Linear")."""
+        for cls, (n, _, _) in self._by_cls.items():
+            if n == name:
+                return self.get(cls)
+        raise KeyError(name)
+
+    def get(self, cls):
+        if cls not in self._generated:
+            name, base, _ = self._by_cls[cls]
+            ns: dict[str, Any] = {"_original_cls": cls, "__module__": __name__}
+            if issubclass(base, QuantLinearConvBase):
+                ns["weight"] = property(_weight_get, _weight_set)
+            self._generated[cls] = type(f"Quant{cls.__name__}", (base, cls), ns)
+        return self._generated[cls]
+
+    @torch.no_grad()
+    def convert(self, module: nn.Module) -> nn.Module:
+        cls = type(module)
+        _, _, pre = self._by_cls[cls]
+        if pre is not None:
+            return pre(module, self)
+        module.__class__ = self.get(cls)
+        module._setup()
+        if module.parallel_state is None:
+            module.parallel_state = ParallelState(data_parallel_group=None)
+        return module
+
+
+QuantModuleRegistry = _Registry()
+QuantModuleRegistry.register({nn.Linear: "nn.Linear"})(_QuantLinear)
+QuantModuleRegistry.register({nn.Conv1d: "nn.Conv1d", nn.Conv2d: "nn.Conv2d", nn.Conv3d: "nn.Conv3d",
+                              nn.ConvTranspose1d: "nn.ConvTranspose1d", nn.ConvTranspose2d: "nn.ConvTranspose2d",
+                              nn.ConvTranspose3d: "nn.ConvTranspose3d"})(_QuantConv)
+QuantModuleRegistry.register({
+    nn.LeakyReLU: "nn.LeakyReLU", nn.BatchNorm1d: "nn.BatchNorm1d", nn.BatchNorm2d: "nn.BatchNorm2d",
+    nn.BatchNorm3d: "nn.BatchNorm3d", nn.InstanceNorm1d: "nn.InstanceNorm1d", nn.InstanceNorm2d: "nn.InstanceNorm2d",
+    nn.InstanceNorm3d: "nn.InstanceNorm3d", nn.LayerNorm: "nn.LayerNorm", nn.MaxPool1d: "nn.MaxPool1d",
+    nn.MaxPool2d: "nn.MaxPool2d", nn.MaxPool3d: "nn.MaxPool3d", nn.AvgPool1d: "nn.AvgPool1d",
+    nn.AvgPool2d: "nn.AvgPool2d", nn.AvgPool3d: "nn.AvgPool3d", nn.AdaptiveAvgPool1d: "nn.AdaptiveAvgPool1d",
+    nn.AdaptiveAvgPool2d: "nn.AdaptiveAvgPool2d", nn.AdaptiveAvgPool3d: "nn.AdaptiveAvgPool3d",
+})(QuantInputBase)
+
+
+class _QuantEmbedding(QuantModule):
+    """quant_embedding.py:31-: only the weight is quantized (disabled by the default configs)."""
+
+    def _setup(self):
+        self.weight_quantizer = TensorQuantizer(QUANT_DESC_8BIT_PER_TENSOR)
+
+    def forward(self, input, *args, **kwargs):
+        w = self._parameters["weight"]
+        self._parameters["weight"] = self.weight_quantizer(w)
+        try:
+            return self._original_cls.forward(self, input, *args, **kwargs)
+        finally:
+            self._parameters["weight"] = w
+
+
+QuantModuleRegistry.register({nn.Embedding: "nn.Embedding"})(_QuantEmbedding)
+
+try:  # HF GPT-2's Conv1D is a Linear with a transposed weight (plugins/huggingface.py:559-575)
+    from transformers.pytorch_utils import Conv1D as _HFConv1D
+
+    def _conv1d_to_linear(module, registry):
+        module.weight = nn.Parameter(module.weight.T.contiguous())
+        module.out_features, module.in_features = module.weight.shape
+        module.__class__ = registry.get(nn.Linear)  # nn.Linear.forward, not Conv1D.forward
+        module._setup()
+        module.parallel_state = ParallelState(data_parallel_group=None)
+        return module
+
+    QuantModuleRegistry.register({_HFConv1D: "Conv1D"}, pre_convert=_conv1d_to_linear)(_QuantLinear)
+except Exception:  # noqa: BLE001  (transformers absent or broken: nothing to register)
+    pass

@@ -338,3 +338,71 @@ def qdq_nvfp4_dynamic_host(x: torch.Tensor, global_amax: float, block=16, numeri
                                                     float(global_amax), int(block), _mode(numerics)),
               "mo_qdq_nvfp4_dynamic_host", n=_chunks(x))
     return y
+
+
+# ------------------------------------------------------------------------------------------------
+# Histogram collection and amax searches (csrc/hist.cu, csrc/hist_search.cu)
+# ------------------------------------------------------------------------------------------------
+def hist_into(x, range_max, counts, amax_bits=None, skip_zeros=False):
+    """Add the histogram of |x| over [0, range_max] (torch.histc binning, len(counts) bins) to `counts`
+    (int64 device tensor, exact) and merge max|x| into `amax_bits` (int32 view of an fp32 word) in the same
+    read.  `range_max` is a device fp32 scalar tensor."""
+    _cuda(x, "hist_into")
+    assert counts.dtype == torch.int64 and counts.is_contiguous() and counts.device == x.device
+    assert range_max.dtype == torch.float32 and range_max.numel() == 1 and range_max.device == x.device
+    x = x.contiguous()
+    with _dev(x):
+        _launched(_lib.load().mo_hist(x.data_ptr(), x.numel(), _code(x), range_max.data_ptr(), counts.numel(),
+                                      counts.data_ptr(), amax_bits.data_ptr() if amax_bits is not None else None,
+                                      int(bool(skip_zeros)), _stream(x)), "mo_hist")
+
+
+def hist_percentile_index(counts, percentile: float) -> torch.Tensor:
+    """Device int32 scalar: searchsorted(cumsum(counts / counts.sum()), percentile / 100) (fp64, numpy order)."""
+    _cuda(counts, "hist_percentile_index")
+    if percentile < 0 or percentile > 100:
+        raise ValueError("Invalid percentile. Must be in range 0 <= percentile <= 100.")
+    idx = torch.empty(1, dtype=torch.int32, device=counts.device)
+    with _dev(counts):
+        _launched(_lib.load().mo_hist_percentile(counts.data_ptr(), counts.numel(), float(percentile), idx.data_ptr(),
+                                                 _stream(counts)), "mo_hist_percentile")
+    return idx
+
+
+def hist_mse_index(counts, edges, num_bits, unsigned, stride=1, start_bin=128, as_written=True):
+    """Device int32 scalar k: the chosen candidate is bin start_bin + k*stride (amax = its centre)."""
+    _cuda(counts, "hist_mse_index")
+    fp8 = num_bits == (4, 3)
+    if not fp8 and not (isinstance(num_bits, int) and num_bits >= 0):
+        raise TypeError("Invalid num_bits. num_bits must be a positive integer or tuple (4,3).")
+    n = counts.numel()
+    edges = edges.to(device=counts.device, dtype=torch.float32).contiguous()
+    assert edges.numel() == n + 1
+    ncand = max(0, -(-(n - start_bin) // stride))
+    if ncand == 0:
+        raise ValueError("attempt to get argmin of an empty sequence")
+    loss = torch.empty(ncand, dtype=torch.float64, device=counts.device)
+    idx = torch.empty(1, dtype=torch.int32, device=counts.device)
+    with _dev(counts):
+        _launched(_lib.load().mo_hist_mse(counts.data_ptr(), edges.data_ptr(), n, 8 if fp8 else int(num_bits),
+                                          int(bool(unsigned)), int(fp8), int(bool(as_written)), int(stride),
+                                          int(start_bin), loss.data_ptr(), idx.data_ptr(), _stream(counts)),
+                  "mo_hist_mse", n=2)
+    return idx, loss
+
+
+def hist_entropy_index(counts, num_bits, unsigned, stride=1, start_bin=128):
+    """Device int32 scalar k: the chosen amax is edges[start_bin + k*stride] (LAST minimum of the KL search)."""
+    _cuda(counts, "hist_entropy_index")
+    n = counts.numel()
+    lib = _lib.load()
+    nbytes = lib.mo_hist_entropy_scratch_bytes(n, int(stride), int(start_bin))
+    if nbytes <= 0 or start_bin > n:
+        raise ValueError("attempt to get argmin of an empty sequence")
+    scratch = torch.empty(nbytes, dtype=torch.uint8, device=counts.device)
+    idx = torch.empty(1, dtype=torch.int32, device=counts.device)
+    with _dev(counts):
+        _launched(lib.mo_hist_entropy(counts.data_ptr(), n, int(num_bits), int(bool(unsigned)), int(stride),
+                                      int(start_bin), scratch.data_ptr(), idx.data_ptr(), _stream(counts)),
+                  "mo_hist_entropy", n=3)
+    return idx

@@ -65,6 +65,22 @@ def main():
         bam = ops.reduce_amax(x.view(-1, 16), axis=1).float()
         sc = ops.fp4_scales(bam, am, True)
         report("qdq nvfp4 static (scales given)", 4.25 * n, lambda: ops.qdq_nvfp4_static(x.view(-1, 16), bam, am))
+        from modelopt_b200.calib import HistogramCalibrator
+        hc = HistogramCalibrator(8, None, False)
+        hc.collect(x)
+        report("hist collect (steady state, fused amax)", 2 * n, lambda: hc.collect(x))
+        rm = am.reshape(1).float().contiguous()
+        cnt = torch.zeros(2048, dtype=torch.int64, device="cuda")
+        report("hist kernel only (mo_hist, 2048 bins)", 2 * n, lambda: ops.hist_into(x, rm, cnt))
+        cnt5 = torch.zeros(5000, dtype=torch.int64, device="cuda")
+        report("hist kernel only (mo_hist, 5000 bins)", 2 * n, lambda: ops.hist_into(x, rm, cnt5))
+        xf = x.float()
+        report("REF-style torch: abs+float+max+histc", 2 * n, lambda: torch.histc(x.abs().float(), bins=2048, min=0, max=float(x.abs().float().max())))
+        del xf
+        import time as _t
+        for m, kw in (("percentile", {}), ("mse", {}), ("entropy", {})):
+            torch.cuda.synchronize(); t0 = _t.perf_counter(); v = hc.compute_amax(m, **kw); torch.cuda.synchronize()
+            print(f"hist search {m:10s} ({hc._counts.numel()} bins): {(_t.perf_counter() - t0) * 1e3:8.2f} ms -> {float(v):.4f}", flush=True)
         del y
         ref = os.path.join(ROOT, "oracle", "_ref")
         if os.path.isdir(os.path.join(ref, "modelopt")):
