@@ -154,6 +154,21 @@ int mo_hist_entropy(const uint64_t* counts, int64_t nbins, int num_bits, int is_
                     int start_bin, void* scratch, int32_t* idx_out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * NVFP4 real-quant packer (row a16): replaces NVFP4QTensor.quantize / dequantize
+ * (qtensor/nvfp4_tensor.py:253-407) and the Triton fp4_dequantize (gemm/fp4_kernel.py:54-190).
+ * x: n_blocks * block contiguous elements (last dim already padded to a multiple of `block`,
+ * reduce_block_padding :279).  sf2: device fp32 scalar = amax / (6 * 448) (:204-207).
+ * codes: uint8[n_blocks * block / 2], element 2j in the LOW nibble, nibble = sign << 3 | e2m1 index (:230-250, :337).
+ * sf_out: uint8[n_blocks] E4M3 bit patterns of the per-block scales (:169-201, :32-46); if sf_in != NULL the
+ * given scales are used instead (weights_scaling_factor argument) and sf_out may be NULL.
+ * ---------------------------------------------------------------------------------------------- */
+int mo_nvfp4_pack(const void* x, int64_t n_blocks, int block, int dtype, const float* sf2, const uint8_t* sf_in,
+                  uint8_t* codes, uint8_t* sf_out, void* stream);
+/* fast = 0: value * (sf * sf2) (nvfp4_tensor.py:396-404); fast = 1: (value * sf) * sf2 (Triton fp4_dequantize). */
+int mo_nvfp4_unpack(const uint8_t* codes, const uint8_t* sf, const float* sf2, int64_t n_blocks, int block,
+                    int out_dtype, int fast, void* y, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.
  * ---------------------------------------------------------------------------------------------- */

@@ -31,7 +31,33 @@ def default_numerics() -> int:
     return MO_DIV_IEEE if os.environ.get("MODELOPT_B200_NUMERICS", "gpu").lower() in _CPU_NAMES else MO_DIV_TRITON
 
 
+_OVERRIDE: list = []
+
+
+class numerics:
+    """Context manager: run the enclosed calls in 'gpu' or 'cpu' numerics (see include/modelopt_b200.h)."""
+
+    def __init__(self, mode):
+        self.mode = mode
+
+    def __enter__(self):
+        _OVERRIDE.append(self.mode)
+
+    def __exit__(self, *a):
+        _OVERRIDE.pop()
+
+
+def div_scalar(t: torch.Tensor, c: float) -> torch.Tensor:
+    """``t / c`` as the reference's torch op computes it: CUDA tensors multiply by the fp32 reciprocal of a Python
+    scalar (GPU numerics); CPU tensors divide (CPU numerics: reproduced here with a tensor / tensor division)."""
+    if _mode(None) == MO_DIV_IEEE:
+        return t / torch.tensor(c, dtype=t.dtype, device=t.device)
+    return t / c
+
+
 def _mode(numerics) -> int:
+    if numerics is None and _OVERRIDE:
+        numerics = _OVERRIDE[-1]
     if numerics is None:
         return default_numerics()
     if isinstance(numerics, str):
@@ -406,3 +432,46 @@ def hist_entropy_index(counts, num_bits, unsigned, stride=1, start_bin=128):
                                       int(start_bin), scratch.data_ptr(), idx.data_ptr(), _stream(counts)),
                   "mo_hist_entropy", n=3)
     return idx
+
+
+# ------------------------------------------------------------------------------------------------
+# NVFP4 packer (csrc/pack_nvfp4.cu)
+# ------------------------------------------------------------------------------------------------
+def nvfp4_pack(x, block, sf2, sf=None):
+    """x [..., N] (N % block == 0) -> (codes uint8 [..., N/2], sf float8_e4m3fn [..., N/block]); sf2: fp32 scalar
+    tensor.  With `sf` given (float8_e4m3fn), those block scales are used."""
+    _cuda(x, "nvfp4_pack")
+    x = x.contiguous()
+    n = x.shape[-1]
+    assert n % block == 0 and block % 2 == 0
+    nb = x.numel() // block
+    codes = torch.empty((*x.shape[:-1], n // 2), dtype=torch.uint8, device=x.device)
+    sf2 = _f32_vec(sf2, x)
+    if sf is None:
+        sf_out = torch.empty((*x.shape[:-1], n // block), dtype=torch.float8_e4m3fn, device=x.device)
+        sf_in_ptr = None
+    else:
+        sf_out = sf.to(device=x.device, dtype=torch.float8_e4m3fn).contiguous()
+        assert sf_out.numel() == nb
+        sf_in_ptr = sf_out.data_ptr()
+    with _dev(x):
+        _launched(_lib.load().mo_nvfp4_pack(x.data_ptr(), nb, int(block), _code(x), sf2.data_ptr(), sf_in_ptr,
+                                            codes.data_ptr(), None if sf is not None else sf_out.data_ptr(),
+                                            _stream(x)), "mo_nvfp4_pack")
+    return codes, sf_out
+
+
+def nvfp4_unpack(codes, sf, sf2, block, dtype, fast=False):
+    """Inverse of nvfp4_pack: [..., N/2] uint8 -> [..., N] `dtype`."""
+    _cuda(codes, "nvfp4_unpack")
+    codes = codes.contiguous()
+    sf = sf.contiguous()
+    n = codes.shape[-1] * 2
+    nb = codes.numel() * 2 // block
+    assert sf.numel() == nb and sf.element_size() == 1
+    y = torch.empty((*codes.shape[:-1], n), dtype=dtype, device=codes.device)
+    sf2 = _f32_vec(sf2, codes)
+    with _dev(codes):
+        _launched(_lib.load().mo_nvfp4_unpack(codes.data_ptr(), sf.data_ptr(), sf2.data_ptr(), nb, int(block), _code(y),
+                                              int(bool(fast)), y.data_ptr(), _stream(codes)), "mo_nvfp4_unpack")
+    return y

@@ -1,0 +1,121 @@
+"""CPU, world size 2 (gloo): the data-parallel exchange of calibration statistics — one all-reduce(MAX) over the amax
+arena, MAX + SUM over histograms.  Host logic only: the statistics are written by hand instead of by
+kernels.  Mirrors the reference's tests/unit/torch/quantization/test_dist.py:27-47 (2 gloo ranks, amax ==
+all_reduce(MAX)(amax))."""
+
+import os
+import socket
+import sys
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, fn_name):
+    sys.path[:0] = [ROOT, os.path.join(ROOT, "tensorrt-model-optimizer_b200"), os.path.join(ROOT, "tests")]
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        globals()[fn_name](rank, world)
+    finally:
+        dist.destroy_process_group()
+
+
+def _spawn(fn_name, world=2):
+    mp.spawn(_worker, args=(world, _free_port(), fn_name), nprocs=world, join=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+def _arena_sync(rank, world):
+    from modelopt_b200.arena import AmaxArena
+
+    a = AmaxArena("cpu", capacity=8)  # small on purpose: forces a growth re-allocation
+    s0, s1, s2 = a.alloc(1), a.alloc(5), a.alloc(3)
+    a.amax(s0)[:] = torch.tensor([1.5 + rank])
+    a.amax(s1)[:] = torch.arange(5, dtype=torch.float32) * (1 if rank == 0 else -1) % 7
+    a.amax(s2)[:] = torch.tensor([0.0, float("nan") if rank == 1 else 3.0, float("inf") if rank == 0 else 2.0])
+    want = []
+    for s in (s0, s1, s2):
+        mine = a.amax(s).clone()
+        gathered = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(gathered, mine)
+        want.append(torch.stack(gathered).max(0).values)  # torch.max propagates NaN like the reference
+    a.sync()
+    for s, w in zip((s0, s1, s2), want):
+        got = a.amax(s)
+        assert torch.equal(torch.isnan(got), torch.isnan(w)) and torch.equal(got.nan_to_num(), w.nan_to_num()), (got, w)
+    with pytest.raises(AssertionError, match="nan"):
+        a.check()
+
+
+def _quantize_sync(rank, world):
+    """max_calibrate's exchange with a stub backend standing in for the kernels: every rank 'collects' a different
+    amax by writing its calibrator state directly; after the sync every rank holds the max."""
+    import modelopt_b200 as mtq
+    from modelopt_b200.arena import AmaxArenaPool
+    from torch import nn
+
+    m = nn.Sequential(nn.Linear(8, 8), nn.Linear(8, 4))
+    mtq.replace_quant_module(m)
+    mtq.set_quantizer_by_cfg(m, mtq.INT8_DEFAULT_CFG["quant_cfg"])
+    pool = AmaxArenaPool()
+    mtq.enable_stats_collection(m, pool)
+    qs = [q for q in m.modules() if isinstance(q, mtq.TensorQuantizer) and q._if_calib]
+    assert len(qs) == 4
+    arena = pool.get("cpu")
+    for i, q in enumerate(qs):  # what MaxCalibrator.collect would have left behind
+        cal = q._calibrator
+        n = 8 if q.axis == 0 and i == 1 else (4 if q.axis == 0 else 1)
+        cal._slot, cal._slot_arena = arena.alloc(n), arena
+        cal._shape, cal._dtype = ((n, 1) if q.axis == 0 else ()), torch.float32
+        arena.amax(cal._slot)[:] = torch.arange(1, n + 1, dtype=torch.float32) * (rank + 1) + i
+    pool.sync()
+    pool.check()
+    mtq.finish_stats_collection(m)
+    for i, q in enumerate(qs):
+        n = q.amax.numel()
+        want = torch.arange(1, n + 1, dtype=torch.float32) * world + i
+        assert torch.equal(q.amax.flatten(), want), (i, q.amax)
+        assert q._if_quant and not q._if_calib
+
+
+def _hist_sync(rank, world):
+    import modelopt_b200 as mtq
+    from modelopt_b200.calib import HistogramCalibrator
+    from torch import nn
+
+    m = nn.Sequential(nn.Linear(8, 8))
+    mtq.replace_quant_module(m)
+    mtq.set_quantizer_by_cfg(m, [{"quantizer_name": "*", "enable": False},
+                                 {"quantizer_name": "*input_quantizer", "cfg": {"num_bits": 8, "calibrator": "histogram"}}])
+    cal = m[0].input_quantizer._calibrator
+    assert isinstance(cal, HistogramCalibrator)
+    nb = 2048 if rank == 0 else 2500  # rank 1's range grew
+    cal._counts = torch.arange(nb, dtype=torch.int64) % 7 + rank
+    cal._calib_bin_edges = torch.arange(0, nb + 1, dtype=torch.float32) * 0.5
+    cal._num_bins = nb
+    mine = cal._counts.clone()
+    mtq.sync_histograms(m)
+    assert cal._counts.numel() == 2500 and cal._calib_bin_edges.numel() == 2501
+    other_nb = 2500 if rank == 0 else 2048
+    other = torch.arange(other_nb, dtype=torch.int64) % 7 + (1 - rank)
+    want = torch.zeros(2500, dtype=torch.int64)
+    want[:nb] += mine
+    want[:other_nb] += other
+    assert torch.equal(cal._counts, want)
+    assert float(cal._calib_bin_edges[-1]) == 1250.0
+
+
+@pytest.mark.parametrize("fn", ["_arena_sync", "_quantize_sync", "_hist_sync"])
+def test_world_size_2(fn):
+    _spawn(fn)

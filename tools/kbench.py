@@ -81,6 +81,12 @@ def main():
         for m, kw in (("percentile", {}), ("mse", {}), ("entropy", {})):
             torch.cuda.synchronize(); t0 = _t.perf_counter(); v = hc.compute_amax(m, **kw); torch.cuda.synchronize()
             print(f"hist search {m:10s} ({hc._counts.numel()} bins): {(_t.perf_counter() - t0) * 1e3:8.2f} ms -> {float(v):.4f}", flush=True)
+        from modelopt_b200.qtensor import NVFP4QTensor
+        sf2 = am / 2688.0
+        report("nvfp4 pack (codes + e4m3 scales)", 2.5625 * n, lambda: ops.nvfp4_pack(x, 16, sf2))
+        cq, sfq = ops.nvfp4_pack(x, 16, sf2)
+        report("nvfp4 unpack", 2.5625 * n, lambda: ops.nvfp4_unpack(cq, sfq, sf2, 16, torch.bfloat16))
+        del cq, sfq
         del y
         ref = os.path.join(ROOT, "oracle", "_ref")
         if os.path.isdir(os.path.join(ref, "modelopt")):
