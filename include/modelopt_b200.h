@@ -169,6 +169,23 @@ int mo_nvfp4_unpack(const uint8_t* codes, const uint8_t* sf, const float* sf2, i
                     int out_dtype, int fast, void* y, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Scale searches (row a11): the tensor is read once for every candidate.
+ * ---------------------------------------------------------------------------------------------- */
+/* Replaces Triton nvfp4_fp8_scale_sweep (gemm/nvfp4_fp8_sweep.py:57-162) and the 126-pass Python sweep of
+ * NVFP4MSECalibrator (calib/mse.py:175-311): for each block of `block` elements try the 126 positive finite
+ * E4M3 values c = e4m3/448 (gemm/_fp8_scale_candidates.py:26-31) as scale = c*global_amax/6, keep the FIRST
+ * minimum of sum((|w| - e2m1(|w|/scale)*scale)^2); best_amax[b] = global_amax * c_best (fp32, device). */
+int mo_nvfp4_fp8_scale_sweep(const void* x, int64_t n_blocks, int block, int dtype, const float* global_amax,
+                             float* best_amax, int numerics, void* stream);
+/* Replaces the K fake-quant + mse_loss + reduce passes of MseCalibrator.collect (calib/mse.py:83-119):
+ * losses[k*axis_size + a] += sum over the [outer, axis_size, inner] view of (x - fq(x, cand_amax[k*axis_size + a]))^2,
+ * fp64 accumulators (device, caller zero-fills before the first batch).  cand_amax is the [n_cand, axis_size] fp32
+ * table initial_amax * candidate the caller forms (calib/mse.py:76-81).  fp8 = 1: E4M3; else INT-N. */
+int mo_mse_sweep(const void* x, int64_t outer, int64_t axis_size, int64_t inner, int dtype, const float* cand_amax,
+                 int n_cand, int num_bits, int is_unsigned, int narrow_range, int fp8, int numerics, double* losses,
+                 void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.
  * ---------------------------------------------------------------------------------------------- */

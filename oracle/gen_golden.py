@@ -220,6 +220,50 @@ def gen_quantize():
     print("quantize_cpu.npz", len(g), "arrays")
 
 
+def gen_mse():
+    """MseCalibrator of the reference on CPU (calib/mse.py:31-172) + mtq.quantize(algorithm='mse') end to end."""
+    import copy
+
+    import modelopt.torch.quantization as mtq
+    from modelopt.torch.quantization.calib import MseCalibrator
+    from modelopt.torch.quantization.tensor_quant import fake_tensor_quant, scaled_e4m3
+
+    g = {}
+    gen = torch.Generator().manual_seed(99)
+    w = torch.randn(96, 320, generator=gen) * torch.rand(96, 1, generator=gen) * 3
+    w[5] = 0
+    w[7, 3] = 40.0  # outlier row: the search should clip it
+    g["w"] = to_np(w)
+    fmts = {"int8": lambda x, a: fake_tensor_quant(x, a, None, 8, False, True),
+            "int4": lambda x, a: fake_tensor_quant(x, a, None, 4, False, True),
+            "fp8": lambda x, a: scaled_e4m3(x, a, None, 4, 3)}
+    for fn, f in fmts.items():
+        for an, (axis, amax) in {"tensor": (None, w.abs().max()), "row": (0, w.abs().amax(dim=1, keepdim=True))}.items():
+            if fn == "fp8" and an == "row":
+                amax = amax.clamp(min=1e-3)
+            c = MseCalibrator(amax=amax.clone(), axis=axis, quant_func=f)
+            c.collect(w)
+            c.collect(w * 0.5)  # two batches accumulate
+            g[f"{fn}_{an}_amax0"] = to_np(amax)
+            g[f"{fn}_{an}_losses"] = to_np(torch.stack(c._losses_sum))
+            g[f"{fn}_{an}_best"] = to_np(c.compute_amax())
+    base = _tiny_model()
+    for k, v in base.state_dict().items():
+        g[f"w_{k}"] = to_np(v)
+    batches = [torch.randn(8, 16, 256, generator=gen) * (1 + i) for i in range(2)]
+    for i, b in enumerate(batches):
+        g[f"batch{i}"] = to_np(b)
+    for name in ("INT8_DEFAULT_CFG", "FP8_DEFAULT_CFG", "INT4_BLOCKWISE_WEIGHT_ONLY_CFG"):
+        cfg = copy.deepcopy(getattr(mtq, name))
+        cfg["algorithm"] = {"method": "mse", "step_size": 0.25}
+        m = mtq.quantize(copy.deepcopy(base), cfg, lambda model: [model(b) for b in batches])
+        for n, mod in m.named_modules():
+            if isinstance(mod, mtq.nn.TensorQuantizer) and hasattr(mod, "_amax"):
+                g[f"{name}|{n}|_amax"] = to_np(mod._amax.float())
+    np.savez_compressed(os.path.join(OUT, "mse_cpu.npz"), **g)
+    print("mse_cpu.npz", len(g), "arrays")
+
+
 def gen_hist():
     from modelopt.torch.quantization.calib import HistogramCalibrator
 
@@ -257,6 +301,6 @@ def gen_hist():
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack", "hist", "quantize"]
+    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack", "hist", "quantize", "mse"]
     for w in which:
         globals()["gen_" + w]()

@@ -40,6 +40,36 @@ def adversarial_rows():
     return torch.stack(rows)
 
 
+def gen_sweep():
+    """Reference NVFP4MSECalibrator on the GPU: Triton fast path and the 126-step Python sweep (calib/mse.py:175-311)."""
+    from modelopt.torch.quantization.calib.mse import NVFP4MSECalibrator
+    from modelopt.torch.quantization.tensor_quant import static_blockwise_fp4_fake_quant
+
+    g = {}
+    torch.manual_seed(2024)
+    base = torch.randn(6000, 16) * torch.rand(6000, 1) * 3
+    base[1] = 0
+    base[2] *= 1e-4
+    base[3, 0] = 30.0
+    for dn, dt in DTYPES.items():
+        x = base.to(dt).cuda()
+        bam = x.float().abs().amax(dim=-1)
+        ga = bam.max()
+        g[f"x_{dn}"], g[f"ga_{dn}"] = to_np(x), to_np(ga)
+        for key, flag in (("best", "1"), ("best_py", "0")):
+            os.environ["MODELOPT_NVFP4_TRITON_SWEEP"] = flag
+            cal = NVFP4MSECalibrator(amax=bam, axis=0, global_amax=ga,
+                                     quant_func=lambda t, a: static_blockwise_fp4_fake_quant(t, a, ga))
+            cal.collect(x)
+            g[f"{key}_{dn}"] = to_np(cal.compute_amax())
+        print(f"sweep {dn}: triton vs python differing blocks =",
+              int((g[f'best_{dn}'] != g[f'best_py_{dn}']).sum()), "/", x.shape[0])
+    os.environ.pop("MODELOPT_NVFP4_TRITON_SWEEP", None)
+    out = os.path.join(ROOT, "gpurun_out", "nvfp4_sweep_b200.npz")
+    np.savez_compressed(out, **g)
+    print("wrote", out, len(g), "arrays")
+
+
 def main():
     assert torch.cuda.is_available()
     import modelopt.torch.kernels.quantization.gemm as tk
@@ -90,6 +120,7 @@ def main():
         except Exception as e:  # noqa: BLE001
             print("reference CUDA ext unavailable:", repr(e)[:200])
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    gen_sweep()
     out = os.path.join(ROOT, "gpurun_out", "nvfp4_triton_b200.npz")
     np.savez_compressed(out, **g)
     print("wrote", out, len(g), "arrays")

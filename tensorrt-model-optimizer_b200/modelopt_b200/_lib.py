@@ -37,6 +37,8 @@ SIGNATURES = {
     "mo_hist_entropy": [_p, _i64, _i, _i, _i, _i, _p, _p, _p],
     "mo_nvfp4_pack": [_p, _i64, _i, _i, _p, _p, _p, _p, _p],
     "mo_nvfp4_unpack": [_p, _p, _p, _i64, _i, _i, _i, _p, _p],
+    "mo_nvfp4_fp8_scale_sweep": [_p, _i64, _i, _i, _p, _p, _i, _p],
+    "mo_mse_sweep": [_p, _i64, _i64, _i64, _i, _p, _i, _i, _i, _i, _i, _i, _p, _p],
     "mo_selftest_e2m1": [C.POINTER(C.c_uint64)],
     "mo_selftest_exact_div": [_i, _i, C.c_uint64, C.POINTER(C.c_uint64)],
     "mo_qdq_fp8_host": [_p, _p, _i64, _i, _f, _i],

@@ -154,3 +154,83 @@ def sync_histograms(model: nn.Module, group=None):
 
 def disable_pre_quant_scale_and_resmooth(*a, **k):  # pragma: no cover
     raise NotImplementedError("modelopt_b200: resmoothing is not implemented")
+
+
+# =================================================================================================
+# MSE weight calibration (model_calib.py:639-826)
+# =================================================================================================
+def _mse_quant_func(x, amax, quantizer):
+    """model_calib.py:639-661: fake-quantize ``x`` with a temporary amax."""
+    original = quantizer._amax.clone() if hasattr(quantizer, "_amax") else None
+    quantizer._amax = amax
+    state = (quantizer._if_quant, quantizer._if_calib, quantizer._fake_quant)
+    quantizer._if_quant, quantizer._if_calib, quantizer._fake_quant = True, False, True
+    try:
+        if hasattr(quantizer, "_original_shape"):
+            x = quantizer._reset_to_original_shape(x)
+        xq = quantizer(x)
+        if hasattr(quantizer, "_block_reshape_size"):
+            xq = quantizer._process_for_blockquant(xq)
+    finally:
+        quantizer._if_quant, quantizer._if_calib, quantizer._fake_quant = state
+        if original is not None:
+            quantizer._amax = original
+        else:
+            delattr(quantizer, "_amax")
+    return xq
+
+
+def _make_weight_mse_calibrator(q, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep):
+    """model_calib.py:664-730."""
+    from functools import partial
+
+    from .calib import MseCalibrator, NVFP4MSECalibrator
+
+    if (not isinstance(q, TensorQuantizer) or not q.is_enabled or q._dynamic or q._calibrator is None
+            or getattr(q, "_amax", None) is None):
+        return None
+    initial = q._amax.clone().detach()
+    axis = q._calibrator._axis
+    quant_func = partial(_mse_quant_func, quantizer=q)
+    if fp8_scale_sweep:
+        if q.is_nvfp4_static and q.backend is None and getattr(q, "global_amax", None) is not None:
+            return NVFP4MSECalibrator(amax=initial, axis=axis, global_amax=q.global_amax, quant_func=quant_func)
+        return None
+    fused = None
+    if q.backend is None and q.pre_quant_scale is None and not q.is_nvfp4_static and not q.is_nvfp4_dynamic:
+        if isinstance(q._num_bits, int):
+            fused = {"num_bits": q._num_bits, "unsigned": q._unsigned, "narrow_range": q._narrow_range}
+        elif q._num_bits == (4, 3):
+            fused = {"num_bits": (4, 3)}
+    return MseCalibrator(amax=initial, axis=axis, step_size=step_size, start_multiplier=start_multiplier,
+                         stop_multiplier=stop_multiplier, quant_func=quant_func, fused=fused)
+
+
+@torch.no_grad()
+def mse_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, step_size: float = 0.1,
+                  start_multiplier: float = 0.25, stop_multiplier: float = 4.0, fp8_scale_sweep: bool = False, **_):
+    """model_calib.py:733-826: max-calibrate everything, then refine every weight amax by MSE search."""
+    max_calibrate(model, forward_loop, distributed_sync)
+    seen = set()
+    for module in model.modules():
+        if id(module) in seen or not isinstance(module, QuantModule):
+            continue
+        seen.add(id(module))
+        for weight, q in module.iter_weights_for_calibration():
+            cal = _make_weight_mse_calibrator(q, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep)
+            if cal is None:
+                continue
+            old = q._calibrator
+            q._calibrator = cal
+            q.disable_quant()
+            q.enable_calib()
+            q(weight)
+            if cal.compute_amax() is not None:
+                q.load_calib_amax()
+            q.enable_quant()
+            q.disable_calib()
+            cal.reset()
+            q._calibrator = old
+
+
+__all__ += ["mse_calibrate"]

@@ -475,3 +475,42 @@ def nvfp4_unpack(codes, sf, sf2, block, dtype, fast=False):
         _launched(_lib.load().mo_nvfp4_unpack(codes.data_ptr(), sf.data_ptr(), sf2.data_ptr(), nb, int(block), _code(y),
                                               int(bool(fast)), y.data_ptr(), _stream(codes)), "mo_nvfp4_unpack")
     return y
+
+
+# ------------------------------------------------------------------------------------------------
+# Scale searches (csrc/sweep.cu)
+# ------------------------------------------------------------------------------------------------
+def nvfp4_fp8_scale_sweep(x, global_amax, block_size=16, numerics=None):
+    """Per-block amax (fp32 [n_blocks]) whose FP8-representable scale minimises the NVFP4 squared error."""
+    _cuda(x, "nvfp4_fp8_scale_sweep")
+    if not isinstance(block_size, int) or block_size <= 0:
+        raise ValueError(f"block_size must be a positive int, got {block_size!r}.")
+    if x.numel() % block_size != 0:
+        raise ValueError(f"x.numel() ({x.numel()}) is not divisible by block_size ({block_size}).")
+    x = x.contiguous()
+    nb = x.numel() // block_size
+    ga = _f32_vec(global_amax, x)
+    best = torch.empty(nb, dtype=torch.float32, device=x.device)
+    with _dev(x):
+        _launched(_lib.load().mo_nvfp4_fp8_scale_sweep(x.data_ptr(), nb, block_size, _code(x), ga.data_ptr(),
+                                                       best.data_ptr(), _mode(numerics), _stream(x)),
+                  "mo_nvfp4_fp8_scale_sweep")
+    return best
+
+
+def mse_sweep_into(x, cand_amax, losses, num_bits=8, unsigned=False, narrow_range=False, numerics=None):
+    """losses[k, a] += sum (x - fq(x, cand_amax[k, a]))^2.  `cand_amax` is [K] (per-tensor) or [K, *amax_shape] for a
+    single-axis amax of `x`; `losses` is a float64 [K, axis_size] device tensor."""
+    _cuda(x, "mse_sweep_into")
+    x = x.contiguous()
+    K = cand_amax.shape[0]
+    axis_size, inner = _axis_of(x, cand_amax[0])
+    cand = cand_amax.detach().to(device=x.device, dtype=torch.float32).contiguous()
+    fp8 = num_bits == (4, 3)
+    assert losses.dtype == torch.float64 and losses.is_contiguous() and losses.numel() == K * axis_size
+    outer = x.numel() // (axis_size * inner)
+    with _dev(x):
+        _launched(_lib.load().mo_mse_sweep(x.data_ptr(), outer, axis_size, inner, _code(x), cand.data_ptr(), K,
+                                           8 if fp8 else int(num_bits), int(bool(unsigned)),
+                                           int(bool(narrow_range)), int(fp8), _mode(numerics), losses.data_ptr(),
+                                           _stream(x)), "mo_mse_sweep")
