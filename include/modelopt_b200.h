@@ -186,6 +186,40 @@ int mo_mse_sweep(const void* x, int64_t outer, int64_t axis_size, int64_t inner,
                  void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * SmoothQuant / AWQ-lite support (rows a13, a14) and the fused pre_quant_scale paths of row a5.
+ * ---------------------------------------------------------------------------------------------- */
+/* INT-N fake quant whose amax is the max|.| of every `block` consecutive elements of the data itself
+ * (TensorQuantizer with block_sizes and no calibrated amax: tensor_quantizer.py:736-751 -> reduce_amax on the
+ * [n/block, block] view), with an optional per-column multiply in front (pre_quant_scale, :1143; `prescale` fp32
+ * [cols] holding values of the tensor dtype, cols % block == 0).  Replaces the `w*s -> reshape -> amax -> QDQ` chain
+ * AWQ-lite runs 11x per linear per batch (model_calib.py:1537-1551).  amax_out (nullable): fp32 [n_blocks]. */
+int mo_qdq_int_block_dynamic(const void* x, void* y, int64_t n_blocks, int block, int dtype, const float* prescale,
+                             int64_t cols, int num_bits, int is_unsigned, int narrow_range, float* amax_out,
+                             void* stream);
+/* mo_qdq_int / mo_qdq_fp8 with TensorQuantizer's `inputs * pre_quant_scale` (tensor_quantizer.py:1143) folded into
+ * the same pass: p = T(x * prescale[i % cols]) is quantized instead of x.  prescale: fp32 [cols] holding values of
+ * the tensor dtype, or NULL (then identical to the plain entry points). */
+int mo_qdq_int_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size, int64_t inner,
+                   int num_bits, int is_unsigned, int narrow_range, uint32_t* status, const float* prescale,
+                   int64_t cols, void* stream);
+int mo_qdq_fp8_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size, int64_t inner,
+                   int numerics, const float* prescale, int64_t cols, void* stream);
+/* y = T(x * scale[col]) over a [rows, cols] matrix (y == x allowed), and in the same pass the amax of y:
+ * amax_mode 0 none, 1 per tensor -> amax_bits[0], 2 per row -> amax_bits[row] (bit patterns, merged with max).
+ * Replaces the weight fold + max re-calibration of apply_pre_quant_scale_and_smooth / _apply_weight_pre_quant_scale
+ * (model_calib.py:1208-1270) and the stand-alone `inputs * pre_quant_scale` pass (tensor_quantizer.py:1143). */
+int mo_scale_cols_amax(const void* x, void* y, int64_t rows, int64_t cols, int dtype, const float* scale,
+                       uint32_t* amax_bits, int amax_mode, void* stream);
+/* AWQ get_weight_scale (model_calib.py:1453-1469): partial[s*cols + c] = sum over the rows of split s of
+ * T(|w[r,c]| / T(blockmax(r, c/block) + tiny(T))); the caller adds the `splits` rows and divides by `rows`. */
+int mo_awq_weight_scale(const void* w, int64_t rows, int64_t cols, int dtype, int block, float* partial, int splits,
+                        void* stream);
+/* AWQ get_act_scale (model_calib.py:1471-1472): partial[s*cols + c] = sum over the rows of split s of |x[r,c]|. */
+int mo_abs_col_sum(const void* x, int64_t rows, int64_t cols, int dtype, float* partial, int splits, void* stream);
+/* AWQ update_loss (model_calib.py:1485-1491): acc[0] += mean((T(a - b))^2) (fp64 device accumulator). */
+int mo_sq_diff_mean(const void* a, const void* b, int64_t n, int dtype, double* acc, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.
  * ---------------------------------------------------------------------------------------------- */

@@ -164,9 +164,21 @@ __device__ __forceinline__ void finish_op(IntOp<U>& op) { op.finish(); }
 // The streaming kernel.  kVec = true: 32-byte vectors (x, y 32-byte aligned); tail and the
 // unaligned case run the scalar path.
 // ------------------------------------------------------------------------------------------------
+template <typename T>
+__device__ __forceinline__ float prescaled(const T* x, int64_t i, const float* pre, int64_t cols) {
+  float v = Elem<T>::load(x + i);
+  if (pre != nullptr) {
+    T t;
+    Elem<T>::store(&t, __fmul_rn(v, __ldg(pre + i % cols)));
+    v = Elem<T>::load(&t);
+  }
+  return v;
+}
+
 template <typename T, typename Op>
 __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restrict__ x, T* __restrict__ y,
-                                                              int64_t n, Op op, bool vectorized) {
+                                                              int64_t n, Op op, bool vectorized,
+                                                              const float* __restrict__ pre, int64_t cols) {
   constexpr int E = Elem<T>::kPerVec;
   op.init();
   if (vectorized) {
@@ -189,6 +201,17 @@ __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restric
         if (c < n_vec) {
           float f[E];
           Elem<T>::unpack(v[u], f);
+          if (pre != nullptr) {  // inputs * pre_quant_scale, a T tensor in the reference (tensor_quantizer.py:1143)
+            const float* ps = pre + (c * E) % cols;
+#pragma unroll
+            for (int i = 0; i < E; i += 4) {
+              const float4 s4 = __ldg(reinterpret_cast<const float4*>(ps + i));
+              f[i] = __fmul_rn(f[i], s4.x); f[i + 1] = __fmul_rn(f[i + 1], s4.y);
+              f[i + 2] = __fmul_rn(f[i + 2], s4.z); f[i + 3] = __fmul_rn(f[i + 3], s4.w);
+            }
+            Elem<T>::pack(f, v[u]);
+            Elem<T>::unpack(v[u], f);
+          }
           op.template vec<E>(f, c * E);
           Elem<T>::pack(f, v[u]);
           st_stream(yv + c, v[u]);
@@ -198,24 +221,153 @@ __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restric
     // tail (< E elements)
     if (blockIdx.x == 0) {
       const int64_t i = n_vec * E + threadIdx.x;
-      if (i < n) Elem<T>::store(y + i, op.one(Elem<T>::load(x + i), i));
+      if (i < n) Elem<T>::store(y + i, op.one(prescaled<T>(x, i, pre, cols), i));
     }
   } else {
     for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
-      Elem<T>::store(y + i, op.one(Elem<T>::load(x + i), i));
+      Elem<T>::store(y + i, op.one(prescaled<T>(x, i, pre, cols), i));
   }
   finish_op(op);
 }
 
 template <typename T, typename Op>
-static int launch_stream(const void* x, void* y, int64_t n, Op op, cudaStream_t stream, const char* what) {
+static int launch_stream(const void* x, void* y, int64_t n, Op op, cudaStream_t stream, const char* what,
+                         const float* pre = nullptr, int64_t cols = 1) {
   constexpr int E = Elem<T>::kPerVec;
-  const bool vec = aligned32(x) && aligned32(y) && n >= E;
+  const bool vec = aligned32(x) && aligned32(y) && n >= E &&
+                   (pre == nullptr || (cols % E == 0 && (reinterpret_cast<uintptr_t>(pre) & 15u) == 0));
   int64_t tiles = vec ? (n / E + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll)
                       : (n + kThreads - 1) / kThreads;
   const int grid = persistent_grid(tiles, 8);
-  qdq_stream_kernel<T, Op><<<grid, kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec);
+  qdq_stream_kernel<T, Op><<<grid, kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, pre, cols);
   return check_launch(what);
+}
+
+// ------------------------------------------------------------------------------------------------
+// INT-N with the amax of every `block` consecutive elements taken from the data (TensorQuantizer with block_sizes
+// and no calibrated amax: _get_amax -> reduce_amax on the [n/block, block] view, tensor_quantizer.py:736-751), and an
+// optional per-column multiply in front (pre_quant_scale, :1143).  One pass: read x once, write y once.
+//   p = T(x * pre[col])   amax = max|p| (a T value)   y = T(int_qdq(p, amax))
+// Vector kernel: `L = block / E` adjacent lanes own one block (L a power of two <= 32).
+// ------------------------------------------------------------------------------------------------
+template <typename T, bool kUnsigned>
+__global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                                    int64_t n_vec, int lanes, const float* __restrict__ pre,
+                                                                    int64_t cols, IntOp<kUnsigned> op,
+                                                                    float* __restrict__ amax_out) {
+  constexpr int E = Elem<T>::kPerVec;
+  op.flags = 0;
+  const int64_t tile_vecs = (int64_t)kThreads * kUnroll;
+  const int64_t n_tiles = (n_vec + tile_vecs - 1) / tile_vecs;
+  const V32* xv = reinterpret_cast<const V32*>(x);
+  V32* yv = reinterpret_cast<V32*>(y);
+  for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+    const int64_t base = tile * tile_vecs + threadIdx.x;
+    V32 v[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t c = base + (int64_t)u * kThreads;
+      if (c < n_vec) v[u] = ld_stream(xv + c);
+    }
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) {
+      const int64_t c = base + (int64_t)u * kThreads;
+      const bool live = c < n_vec;
+      float f[E];
+      uint32_t m = 0;
+      if (live) {
+        Elem<T>::unpack(v[u], f);
+        if (pre != nullptr) {
+          const float* ps = pre + (c * E) % cols;
+#pragma unroll
+          for (int i = 0; i < E; i += 4) {
+            const float4 s4 = __ldg(reinterpret_cast<const float4*>(ps + i));
+            f[i] = __fmul_rn(f[i], s4.x); f[i + 1] = __fmul_rn(f[i + 1], s4.y);
+            f[i + 2] = __fmul_rn(f[i + 2], s4.z); f[i + 3] = __fmul_rn(f[i + 3], s4.w);
+          }
+          Elem<T>::pack(f, v[u]);    // the product is a T tensor in the reference
+          Elem<T>::unpack(v[u], f);
+        }
+#pragma unroll
+        for (int i = 0; i < E; ++i) m = max(m, __float_as_uint(f[i]) & 0x7fffffffu);
+      }
+      for (int o = 1; o < lanes; o <<= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
+      if (live) {
+        const float am = __uint_as_float(m);
+        op.set(am);
+#pragma unroll
+        for (int i = 0; i < E; ++i) f[i] = op.q1(f[i]);
+        Elem<T>::pack(f, v[u]);
+        st_stream(yv + c, v[u]);
+        if (amax_out != nullptr && (c & (lanes - 1)) == 0) amax_out[c / lanes] = am;
+      }
+    }
+  }
+}
+
+// Any block size / alignment: one warp per block, two sweeps over the (L1-resident) block.
+template <typename T, bool kUnsigned>
+__global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_generic_kernel(const T* __restrict__ x, T* __restrict__ y,
+                                                                            int64_t n_blocks, int block,
+                                                                            const float* __restrict__ pre, int64_t cols,
+                                                                            IntOp<kUnsigned> op,
+                                                                            float* __restrict__ amax_out) {
+  op.flags = 0;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * kThreads + threadIdx.x) >> 5;
+  const int64_t n_warps = ((int64_t)gridDim.x * kThreads) >> 5;
+  for (int64_t b = warp; b < n_blocks; b += n_warps) {
+    const int64_t e0 = b * block;
+    uint32_t m = 0;
+    for (int i = lane; i < block; i += 32) {
+      float p = Elem<T>::load(x + e0 + i);
+      if (pre != nullptr) {
+        T t;
+        Elem<T>::store(&t, __fmul_rn(p, __ldg(pre + (e0 + i) % cols)));
+        p = Elem<T>::load(&t);
+      }
+      m = max(m, __float_as_uint(p) & 0x7fffffffu);
+    }
+    m = warp_max_u32(m);
+    const float am = __uint_as_float(m);
+    op.set(am);
+    for (int i = lane; i < block; i += 32) {
+      float p = Elem<T>::load(x + e0 + i);
+      if (pre != nullptr) {
+        T t;
+        Elem<T>::store(&t, __fmul_rn(p, __ldg(pre + (e0 + i) % cols)));
+        p = Elem<T>::load(&t);
+      }
+      Elem<T>::store(y + e0 + i, op.q1(p));
+    }
+    if (amax_out != nullptr && lane == 0) amax_out[b] = am;
+  }
+}
+
+template <typename T, bool U>
+static int blockdyn_launch(const void* x, void* y, int64_t n_blocks, int block, const float* pre, int64_t cols,
+                           int num_bits, int narrow_range, float* amax_out, cudaStream_t s) {
+  constexpr int E = Elem<T>::kPerVec;
+  IntOp<U> op;
+  const float bound = (float)((1 << (num_bits - 1 + (U ? 1 : 0))) - 1);
+  op.maxb = bound;
+  op.minb = -(bound + (narrow_range ? 0.f : 1.f));
+  op.status = nullptr;
+  op.ax.mode = kPerElem;  // scale is set per block by the kernel
+  op.ax.amax = nullptr; op.ax.axis_size = 1; op.ax.inner = 1;
+  const int lanes = block / E;
+  const bool vec = aligned32(x) && aligned32(y) && block % E == 0 && lanes >= 1 && lanes <= 32 &&
+                   (lanes & (lanes - 1)) == 0 && (pre == nullptr || (cols % E == 0 && (reinterpret_cast<uintptr_t>(pre) & 15u) == 0));
+  if (vec) {
+    const int64_t n_vec = n_blocks * lanes;
+    const int64_t tiles = (n_vec + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll);
+    qdq_int_blockdyn_kernel<T, U><<<persistent_grid(tiles, 8), kThreads, 0, s>>>(
+        static_cast<const T*>(x), static_cast<T*>(y), n_vec, lanes, pre, cols, op, amax_out);
+  } else {
+    qdq_int_blockdyn_generic_kernel<T, U><<<persistent_grid((n_blocks * 32 + kThreads - 1) / kThreads, 8), kThreads, 0, s>>>(
+        static_cast<const T*>(x), static_cast<T*>(y), n_blocks, block, pre, cols, op, amax_out);
+  }
+  return check_launch("mo_qdq_int_block_dynamic");
 }
 
 static int make_axis(AxisArgs& ax, const float* amax, int64_t n, int64_t axis_size, int64_t inner, int per_vec) {
@@ -236,10 +388,16 @@ static int make_axis(AxisArgs& ax, const float* amax, int64_t n, int64_t axis_si
 
 using namespace mo;
 
-extern "C" int mo_qdq_fp8(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
-                          int64_t inner, int numerics, void* stream) {
+static int check_pre(const float* pre, int64_t cols, int64_t n, const char* what) {
+  if (pre && (cols < 1 || n % cols != 0)) { set_error("%s: cols=%lld must divide n=%lld", what, (long long)cols, (long long)n); return MO_ERR_SHAPE; }
+  return MO_OK;
+}
+
+extern "C" int mo_qdq_fp8_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
+                              int64_t inner, int numerics, const float* prescale, int64_t cols, void* stream) {
   if (n == 0) return MO_OK;
   if (!x || !y) { set_error("mo_qdq_fp8: x/y is NULL"); return MO_ERR_NULL; }
+  if (int rc0 = check_pre(prescale, cols, n, "mo_qdq_fp8_pqs")) return rc0;
   Fp8Op op;
   op.plain = amax == nullptr;
   op.eager = numerics == MO_NUMERICS_CPU;
@@ -248,19 +406,25 @@ extern "C" int mo_qdq_fp8(const void* x, void* y, int64_t n, int dtype, const fl
   int rc;
   switch (dtype) {
     case MO_F32:  if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 8))) return rc;
-                  return launch_stream<float, Fp8Op>(x, y, n, op, s, "mo_qdq_fp8<f32>");
+                  return launch_stream<float, Fp8Op>(x, y, n, op, s, "mo_qdq_fp8<f32>", prescale, cols);
     case MO_F16:  if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 16))) return rc;
-                  return launch_stream<__half, Fp8Op>(x, y, n, op, s, "mo_qdq_fp8<f16>");
+                  return launch_stream<__half, Fp8Op>(x, y, n, op, s, "mo_qdq_fp8<f16>", prescale, cols);
     case MO_BF16: if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 16))) return rc;
-                  return launch_stream<__nv_bfloat16, Fp8Op>(x, y, n, op, s, "mo_qdq_fp8<bf16>");
+                  return launch_stream<__nv_bfloat16, Fp8Op>(x, y, n, op, s, "mo_qdq_fp8<bf16>", prescale, cols);
   }
   set_error("mo_qdq_fp8: unsupported dtype %d", dtype);
   return MO_ERR_DTYPE;
 }
 
+extern "C" int mo_qdq_fp8(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
+                          int64_t inner, int numerics, void* stream) {
+  return mo_qdq_fp8_pqs(x, y, n, dtype, amax, axis_size, inner, numerics, nullptr, 1, stream);
+}
+
 template <bool U>
 static int qdq_int_impl(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
-                        int64_t inner, int num_bits, int narrow_range, uint32_t* status, cudaStream_t s) {
+                        int64_t inner, int num_bits, int narrow_range, uint32_t* status, cudaStream_t s,
+                        const float* pre, int64_t cols) {
   IntOp<U> op;
   const float bound = (float)((1 << (num_bits - 1 + (U ? 1 : 0))) - 1);  // tensor_quant_gpu.cu:38-41
   op.maxb = bound;
@@ -269,26 +433,58 @@ static int qdq_int_impl(const void* x, void* y, int64_t n, int dtype, const floa
   int rc;
   switch (dtype) {
     case MO_F32:  if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 8))) return rc;
-                  return launch_stream<float, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<f32>");
+                  return launch_stream<float, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<f32>", pre, cols);
     case MO_F16:  if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 16))) return rc;
-                  return launch_stream<__half, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<f16>");
+                  return launch_stream<__half, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<f16>", pre, cols);
     case MO_BF16: if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 16))) return rc;
-                  return launch_stream<__nv_bfloat16, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<bf16>");
+                  return launch_stream<__nv_bfloat16, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<bf16>", pre, cols);
   }
   set_error("mo_qdq_int: unsupported dtype %d", dtype);
   return MO_ERR_DTYPE;
 }
 
-extern "C" int mo_qdq_int(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
-                          int64_t inner, int num_bits, int is_unsigned, int narrow_range, uint32_t* status,
-                          void* stream) {
+extern "C" int mo_qdq_int_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
+                              int64_t inner, int num_bits, int is_unsigned, int narrow_range, uint32_t* status,
+                              const float* prescale, int64_t cols, void* stream) {
   if (n == 0) return MO_OK;
+  if (int rc0 = check_pre(prescale, cols, n, "mo_qdq_int_pqs")) return rc0;
   if (!x || !y || !amax) { set_error("mo_qdq_int: x/y/amax is NULL"); return MO_ERR_NULL; }
   if (num_bits < 1 || num_bits + (is_unsigned ? 1 : 0) > 22) {
     set_error("mo_qdq_int: num_bits=%d out of range [1, 22 - unsigned]", num_bits);
     return MO_ERR_ARG;
   }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  return is_unsigned ? qdq_int_impl<true>(x, y, n, dtype, amax, axis_size, inner, num_bits, narrow_range, status, s)
-                     : qdq_int_impl<false>(x, y, n, dtype, amax, axis_size, inner, num_bits, narrow_range, status, s);
+  return is_unsigned ? qdq_int_impl<true>(x, y, n, dtype, amax, axis_size, inner, num_bits, narrow_range, status, s, prescale, cols)
+                     : qdq_int_impl<false>(x, y, n, dtype, amax, axis_size, inner, num_bits, narrow_range, status, s, prescale, cols);
+}
+
+extern "C" int mo_qdq_int(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
+                          int64_t inner, int num_bits, int is_unsigned, int narrow_range, uint32_t* status,
+                          void* stream) {
+  return mo_qdq_int_pqs(x, y, n, dtype, amax, axis_size, inner, num_bits, is_unsigned, narrow_range, status, nullptr, 1,
+                        stream);
+}
+
+extern "C" int mo_qdq_int_block_dynamic(const void* x, void* y, int64_t n_blocks, int block, int dtype,
+                                        const float* prescale, int64_t cols, int num_bits, int is_unsigned,
+                                        int narrow_range, float* amax_out, void* stream) {
+  if (n_blocks == 0) return MO_OK;
+  if (!x || !y) { set_error("mo_qdq_int_block_dynamic: x/y is NULL"); return MO_ERR_NULL; }
+  if (n_blocks < 0 || block < 1) { set_error("mo_qdq_int_block_dynamic: bad n_blocks / block"); return MO_ERR_SHAPE; }
+  if (prescale && (cols < 1 || cols % block != 0)) {
+    set_error("mo_qdq_int_block_dynamic: cols=%lld must be a positive multiple of block=%d", (long long)cols, block);
+    return MO_ERR_SHAPE;
+  }
+  if (num_bits < 1 || num_bits + (is_unsigned ? 1 : 0) > 22) { set_error("mo_qdq_int_block_dynamic: bad num_bits"); return MO_ERR_ARG; }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+#define MO_BD(T) (is_unsigned ? blockdyn_launch<T, true>(x, y, n_blocks, block, prescale, cols, num_bits, narrow_range, amax_out, s) \
+                              : blockdyn_launch<T, false>(x, y, n_blocks, block, prescale, cols, num_bits, narrow_range, amax_out, s))
+  switch (dtype) {
+    case MO_F32: return MO_BD(float);
+    case MO_F16: return MO_BD(__half);
+    case MO_BF16: return MO_BD(__nv_bfloat16);
+  }
+#undef MO_BD
+  set_error("mo_qdq_int_block_dynamic: unsupported dtype %d", dtype);
+  return MO_ERR_DTYPE;
 }

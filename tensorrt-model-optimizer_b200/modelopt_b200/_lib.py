@@ -39,6 +39,13 @@ SIGNATURES = {
     "mo_nvfp4_unpack": [_p, _p, _p, _i64, _i, _i, _i, _p, _p],
     "mo_nvfp4_fp8_scale_sweep": [_p, _i64, _i, _i, _p, _p, _i, _p],
     "mo_mse_sweep": [_p, _i64, _i64, _i64, _i, _p, _i, _i, _i, _i, _i, _i, _p, _p],
+    "mo_qdq_int_block_dynamic": [_p, _p, _i64, _i, _i, _p, _i64, _i, _i, _i, _p, _p],
+    "mo_qdq_int_pqs": [_p, _p, _i64, _i, _p, _i64, _i64, _i, _i, _i, _p, _p, _i64, _p],
+    "mo_qdq_fp8_pqs": [_p, _p, _i64, _i, _p, _i64, _i64, _i, _p, _i64, _p],
+    "mo_scale_cols_amax": [_p, _p, _i64, _i64, _i, _p, _p, _i, _p],
+    "mo_awq_weight_scale": [_p, _i64, _i64, _i, _i, _p, _i, _p],
+    "mo_abs_col_sum": [_p, _i64, _i64, _i, _p, _i, _p],
+    "mo_sq_diff_mean": [_p, _p, _i64, _i, _p, _p],
     "mo_selftest_e2m1": [C.POINTER(C.c_uint64)],
     "mo_selftest_exact_div": [_i, _i, C.c_uint64, C.POINTER(C.c_uint64)],
     "mo_qdq_fp8_host": [_p, _p, _i64, _i, _f, _i],

@@ -4,6 +4,7 @@
 
 from __future__ import annotations
 
+import contextlib
 import fnmatch
 import re
 from collections.abc import Callable
@@ -16,7 +17,7 @@ from .nn.quant_module import QuantModuleRegistry
 from .nn.tensor_quantizer import SequentialQuantizer, TensorQuantizer
 from .utils import is_quantized
 
-__all__ = ["replace_quant_module", "set_quantizer_by_cfg", "set_quantizer_attribute", "set_quantizer_attributes_full",
+__all__ = ["replace_quant_module", "set_quantizer_by_cfg", "set_quantizer_by_cfg_context", "set_quantizer_attribute", "set_quantizer_attributes_full",
            "set_quantizer_attributes_partial", "quantizer_state", "restore_quantizer_state"]
 
 _EXPERT_LIST_RE = re.compile(r"(weight_quantizers?|input_quantizers?)\.\d+(?=$|\.)")
@@ -119,6 +120,26 @@ def set_quantizer_by_cfg(model: nn.Module, quant_cfg):
             attrs = [c.model_copy(update={"enable": enable}) if isinstance(c, QuantizerAttributeConfig)
                      else QuantizerAttributeConfig(**c, enable=enable) for c in cfg]
             set_quantizer_attributes_full(model, name, attrs, parent_class)
+
+
+@contextlib.contextmanager
+def set_quantizer_by_cfg_context(model: nn.Module, quant_cfg):
+    """conversion.py:507-599: apply ``quant_cfg`` for the duration of the context, then put every TensorQuantizer's
+    properties (not its buffers or calibrator objects) back."""
+    quant_cfg = normalize_quant_cfg_list(quant_cfg)
+    for entry in quant_cfg:
+        if isinstance(entry.get("cfg"), list):
+            raise ValueError("Sequential cfg lists are not allowed in set_quantizer_by_cfg_context. "
+                             "Use only single-dict cfg entries.")
+    saved = {n: m.get_modelopt_state(properties_only=True) for n, m in model.named_modules()
+             if isinstance(m, TensorQuantizer)}
+    try:
+        set_quantizer_by_cfg(model, quant_cfg)
+        yield
+    finally:
+        for n, m in model.named_modules():
+            if isinstance(m, TensorQuantizer) and n in saved:
+                m.set_from_modelopt_state(saved[n], properties_only=True)
 
 
 def quantizer_state(model: nn.Module) -> dict[str, Any]:

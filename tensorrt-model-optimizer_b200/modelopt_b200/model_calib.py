@@ -234,3 +234,357 @@ def mse_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, st
 
 
 __all__ += ["mse_calibrate"]
+
+
+# =================================================================================================
+# SmoothQuant (model_calib.py:1208-1359)
+# =================================================================================================
+def _recalibrate_weight(linear):
+    """reset_amax + max-calibrate the weight quantizer on the current weight (model_calib.py:1222-1223)."""
+    q = linear.weight_quantizer
+    q.reset_amax()
+    max_calibrate(linear, lambda lin: lin.weight_quantizer(lin.weight), distributed_sync=False)
+
+
+@torch.no_grad()
+def _apply_weight_pre_quant_scale(linear, pre_quant_scale):
+    """W <- dtype(W * s[None, :]) and the weight amax of the result.  Per-row / per-tensor weight quantizers get both
+    from ONE kernel (mo_scale_cols_amax); other layouts fold with that kernel and re-calibrate with mo_amax."""
+    from . import ops
+
+    w = linear.weight
+    s = pre_quant_scale.to(w.device).squeeze()
+    q = linear.weight_quantizer
+    mode = None
+    if (isinstance(q, TensorQuantizer) and q.is_enabled and q.block_sizes is None and not q._dynamic
+            and isinstance(q._calibrator, MaxCalibrator) and w.is_cuda and w.dim() == 2 and w.is_contiguous()):
+        mode = "row" if q.axis in (0, (0,)) else ("tensor" if q.axis is None else None)
+    if not (w.is_cuda and w.dim() == 2 and w.is_contiguous()):
+        w.data.copy_((w * s[None, :]).to(w.dtype))
+        _recalibrate_weight(linear)
+        return
+    if mode is None:
+        ops.scale_cols(w.data, s, out=w.data)
+        _recalibrate_weight(linear)
+        return
+    bits = torch.zeros(w.shape[0] if mode == "row" else 1, dtype=torch.int32, device=w.device)
+    ops.scale_cols(w.data, s, out=w.data, amax_bits=bits, amax_mode=mode)
+    amax = bits.view(torch.float32)
+    amax = amax.view(-1, 1) if mode == "row" else amax.reshape(())
+    q.reset_amax()
+    q.amax = amax.to(w.dtype)
+    linear.__dict__.pop("_weight_collect_key", None)
+
+
+@torch.no_grad()
+def apply_pre_quant_scale_and_smooth(linear: nn.Module, pre_quant_scale: torch.Tensor | None = None):
+    """model_calib.py:1226-1270."""
+    from .utils import is_quantized_linear
+
+    assert is_quantized_linear(linear), "Only quantized linear modules are supported"
+    assert linear.input_quantizer.pre_quant_scale is None, "pre_quant_scale should be None first!"
+    if pre_quant_scale is None:
+        pre_quant_scale = getattr(linear.input_quantizer, "_pre_quant_scale", None)
+    assert pre_quant_scale is not None, "pre_quant_scale should be provided or already set"
+    assert torch.all(pre_quant_scale > 0), "pre_quant_scale should be positive"
+    pre_quant_scale = pre_quant_scale.to(torch.float32)
+    iq = linear.input_quantizer
+    iq._enable_pre_quant_scale = True
+    iq.pre_quant_scale = pre_quant_scale.to(linear.weight.dtype)
+    _apply_weight_pre_quant_scale(linear, 1.0 / pre_quant_scale)
+    if iq.amax is not None:
+        assert hasattr(iq, "_amax_for_smoothing")
+        device, dtype = linear.weight.device, linear.weight.dtype
+        a = iq._amax_for_smoothing.to(device=device, dtype=dtype)
+        iq.amax = (a * pre_quant_scale.to(device)).amax().to(dtype)
+
+
+@torch.no_grad()
+def smoothquant(model: nn.Module, forward_loop=None, alpha=1.0, **_):
+    """model_calib.py:1273-1359."""
+    from .utils import is_quantized_linear
+
+    assert forward_loop is not None, "forward_loop must be provided for smoothquant"
+    for module in model.modules():
+        if is_quantized_linear(module) and module.input_quantizer.is_enabled and module.input_quantizer.axis is None:
+            module.input_quantizer.axis = -1
+    max_calibrate(model, forward_loop)
+    smoothed = 0
+    for name, module in model.named_modules():
+        if not is_quantized_linear(module):
+            continue
+        iq, wq = module.input_quantizer, module.weight_quantizer
+        if not hasattr(iq, "_amax"):
+            warnings.warn(f"{name} is not calibrated, skip smoothing")
+            continue
+        if iq.num_bits != 8 or wq.num_bits != 8:
+            warnings.warn(f"Only int8 smoothing is supported, skip {name}")
+            continue
+        if iq.axis != -1:
+            warnings.warn(f"Only per-channel smoothing is supported, skip {name}")
+            continue
+        assert iq._amax.numel() > 1, f"Error: {name} has only one channel to smooth"
+        from .utils import reduce_amax
+
+        act_amax = iq.amax.float()
+        w = module.weight
+        weight_scale = reduce_amax(w.detach(), axis=0, keepdims=True)  # column max of |W| (one mo_amax launch)
+        device, dtype = w.device, w.dtype
+        scale_a = (weight_scale.pow(1 - alpha) / act_amax.pow(alpha)).squeeze()
+        iq._amax_for_smoothing = act_amax.cpu()
+        iq.reset_amax()
+        iq.axis = None
+        iq.amax = act_amax.amax().to(dtype=dtype, device=device)
+        epsilon = 1.0 / (1 << 31)
+        if scale_a.min() <= epsilon:
+            scale_a[(act_amax <= epsilon).reshape(-1)] = 1
+        scale_a = scale_a.clamp(min=1e-4, max=1e4)
+        apply_pre_quant_scale_and_smooth(module, scale_a)
+        smoothed += 1
+    print(f"Smoothed {smoothed} modules")
+
+
+__all__ += ["smoothquant", "apply_pre_quant_scale_and_smooth"]
+
+
+# =================================================================================================
+# AWQ-lite (model_calib.py:1362-1721)
+# =================================================================================================
+def _get_awq_quantizer_block_size(tensor, quantizer):
+    """model_calib.py:1943-1952."""
+    if quantizer.block_sizes is None:
+        return None
+    if -1 in quantizer.block_sizes:
+        return quantizer.block_sizes[-1]
+    if 1 in quantizer.block_sizes:
+        return quantizer.block_sizes[1]
+    raise ValueError("AWQ requires block quantization along -1 axis")
+
+
+def _awq_weight_scale(weight, block_size):
+    """get_weight_scale (model_calib.py:1453-1469): ONE kernel when the block tiles the row, else the eager chain."""
+    from . import ops
+
+    per_vec = 8 if weight.dtype == torch.float32 else 16
+    cols = weight.shape[-1]
+    block = block_size or cols
+    lanes = block // per_vec
+    if (weight.is_cuda and weight.dtype in (torch.float32, torch.float16, torch.bfloat16) and cols % block == 0
+            and block % per_vec == 0 and 1 <= lanes <= 32 and lanes & (lanes - 1) == 0
+            and weight.data_ptr() % 32 == 0):
+        return ops.awq_weight_scale(weight.detach(), block)
+    org_shape, sl, w = weight.shape, None, weight
+    if block_size:
+        if org_shape[-1] % block_size != 0:
+            sl = slice(org_shape[-1])
+            w = torch.nn.functional.pad(w, (0, block_size - org_shape[-1] % block_size), "constant", 0)
+            org_shape = w.shape
+        w = w.contiguous().view(-1, block_size)
+    wa = w.abs()
+    scale = (wa / (wa.amax(dim=1, keepdim=True) + torch.finfo(w.dtype).tiny)).view(org_shape)
+    if sl is not None:
+        scale = scale[..., sl]
+    return scale.mean(0).to(torch.float32)
+
+
+def _awq_act_scale(x):
+    """get_act_scale (model_calib.py:1471-1472)."""
+    from . import ops
+
+    per_vec = 8 if x.dtype == torch.float32 else 16
+    if x.is_cuda and x.dtype in (torch.float32, torch.float16, torch.bfloat16) and x.shape[-1] % per_vec == 0 \
+            and x.is_contiguous() and x.data_ptr() % 32 == 0:
+        return ops.awq_act_scale(x.detach())
+    return x.abs().contiguous().view(-1, x.shape[-1]).mean(0).to(torch.float32)
+
+
+def _awq_get_scale(x_max, w_max, alpha):
+    """get_scale (model_calib.py:1474-1483); [Cin] vectors, stays in torch."""
+    scales = (x_max.pow(alpha) / (w_max.to(x_max.device).pow(1 - alpha) + torch.finfo(torch.float32).tiny)) \
+        .clamp(min=1e-4, max=1e4).view(-1)
+    return (scales / (scales.max() * scales.min()).sqrt()).view(-1)
+
+
+class AWQLiteHelper:
+    """Per-linear search state (model_calib.py:1414-1451).  Losses are fp64 device accumulators, one per alpha; the
+    11 candidate scale vectors are formed once when the search pass starts, not once per batch."""
+
+    cache_mode: bool = False
+
+    def __init__(self, module, name, alpha_step):
+        self.name = name
+        self.act_scale = 0.0
+        self.num_cache_steps = 0
+        self.num_search_steps = 0
+        self.block_size = _get_awq_quantizer_block_size(module.weight, module.weight_quantizer)
+        self.weight_scale = _awq_weight_scale(module.weight, self.block_size)
+        self.alphas = [k.item() for k in torch.arange(0, 1.0 + alpha_step, alpha_step)]
+        self.loss_acc = torch.zeros(len(self.alphas), dtype=torch.float64, device=module.weight.device)
+        self.loss = dict.fromkeys(self.alphas, 0.0)
+        self.scales = None
+        self.best_scale = None
+        self.best_alpha = None
+        self.is_input_quantized = module.input_quantizer.is_enabled
+        self.num_tokens = 0
+        self.module = module
+        self.is_enabled = True
+
+    def setup(self):
+        module = self.module
+        module.__dict__["_forward_no_awq"] = module.forward
+        module.forward = _awq_lite_forward.__get__(module)
+        if module.input_quantizer.is_enabled:
+            module.input_quantizer.disable()
+            if module.input_quantizer.axis not in [None, -1]:
+                self.is_enabled = False
+                return
+            module.input_quantizer.axis = -1
+
+    def cleanup(self):
+        module = self.module
+        module.__dict__.pop("_if_calib", None)
+        module.__dict__.pop("forward", None)
+        module.__dict__.pop("_forward_no_awq", None)
+
+
+def _awq_lite_forward(self, input, *args, **kwargs):
+    """The search forward (model_calib.py:1507-1560)."""
+    from . import ops
+
+    h = self.awq_lite
+    self.weight_quantizer.disable()
+    for q in (self.input_quantizer, self.weight_quantizer):
+        if hasattr(q, "_pre_quant_scale"):
+            delattr(q, "_pre_quant_scale")
+    out_actual = self._forward_no_awq(input, *args, **kwargs)
+    self.weight_quantizer.enable()
+    if input.numel() == 0 or not h.is_enabled:
+        return out_actual
+    if AWQLiteHelper.cache_mode:
+        h.act_scale = h.act_scale + _awq_act_scale(self.input_quantizer(input))
+        h.num_cache_steps += 1
+        h.num_tokens += input.numel() / input.shape[-1]
+        if h.is_input_quantized:
+            self.input_quantizer._calibrator.collect(input)  # running per-channel amax (one mo_amax launch)
+        return out_actual
+    if h.scales is None:
+        h.scales = []
+        for alpha in h.alphas:
+            s = _awq_get_scale(h.act_scale, h.weight_scale, alpha)
+            h.scales.append(((1 / s).to(self.weight.dtype), s.to(self.weight.dtype)))
+    ref = out_actual[0] if isinstance(out_actual, tuple) else out_actual
+    self.input_quantizer._enable_pre_quant_scale = True
+    self.weight_quantizer._enable_pre_quant_scale = True
+    for k, (inv_s, s) in enumerate(h.scales):
+        self.input_quantizer.pre_quant_scale = inv_s
+        self.weight_quantizer.pre_quant_scale = s
+        out = self._forward_no_awq(input, *args, **kwargs)
+        out = out[0] if isinstance(out, tuple) else out
+        if out.is_cuda and out.dtype == ref.dtype and out.dtype != torch.float64:
+            ops.sq_diff_mean_into(out, ref, h.loss_acc[k:k + 1])  # one kernel, no host sync
+        else:
+            h.loss_acc[k] += (out - ref).float().pow(2).mean().double()
+    h.num_search_steps += 1
+    return out_actual
+
+
+@torch.no_grad()
+def awq_lite(model: nn.Module, forward_loop=None, alpha_step: float = 0.1, debug: bool = False, **_):
+    """model_calib.py:1394-1721 (single-GPU / data-parallel; tensor- and expert-parallel syncs are out of scope)."""
+    from .conversion import set_quantizer_by_cfg_context
+    from .utils import is_quantized_linear
+
+    if forward_loop is None:
+        warnings.warn("forward_loop must be provided for awq_lite; skipping awq_lite")
+        return
+    helpers = []
+    for name, module in model.named_modules():
+        if is_quantized_linear(module) and module.weight_quantizer.is_enabled:
+            module.awq_lite = AWQLiteHelper(module, name, alpha_step)
+            module.awq_lite.setup()
+            helpers.append((name, module))
+
+    AWQLiteHelper.cache_mode = True
+    enable_stats_collection(model)
+    forward_loop(model)
+    for _, module in helpers:  # input quantizers were collected directly by the patched forward
+        h, iq = module.awq_lite, module.input_quantizer
+        if h.is_input_quantized and h.num_cache_steps > 0 and iq._calibrator.compute_amax() is not None:
+            iq.load_calib_amax()
+    with set_quantizer_by_cfg_context(model, [{"quantizer_name": "*weight_quantizer", "enable": False}]):
+        max_calibrate(model, lambda m: None, distributed_sync=True)
+    finish_stats_collection(model)
+
+    world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+    for _, module in helpers:
+        h = module.awq_lite
+        if h.num_cache_steps > 0:
+            module.__dict__["_if_calib"] = True
+            h.act_scale = h.act_scale / h.num_cache_steps
+            bad = bool(torch.any(torch.isnan(h.act_scale)) or torch.any(torch.isnan(h.weight_scale)))
+            if world > 1:
+                flag = torch.tensor([float(bad)], device=h.act_scale.device)
+                dist.all_reduce(flag, op=dist.ReduceOp.MAX)
+                bad = bool(flag.item())
+            if bad:
+                h.is_enabled = False
+            elif world > 1:
+                dist.all_reduce(h.act_scale, op=dist.ReduceOp.SUM)
+                h.act_scale /= world
+        else:
+            h.is_enabled = False
+
+    AWQLiteHelper.cache_mode = False
+    forward_loop(model)
+
+    for name, module in helpers:
+        h, iq = module.awq_lite, module.input_quantizer
+        if h.num_cache_steps > 0 and h.num_search_steps == 0:
+            h.is_enabled = False
+            warnings.warn(f"awq_lite: Calling `forward_loop(model)` the second time did not forward data through the "
+                          f"{name}. Please provide a valid `forward_loop` function that can be used to forward data "
+                          "through the model many times.")
+        for q in (module.weight_quantizer, iq):
+            if hasattr(q, "_pre_quant_scale"):
+                delattr(q, "_pre_quant_scale")
+        if h.is_input_quantized:
+            if iq.amax is not None:
+                act_amax = iq.amax
+                iq._amax_for_smoothing = act_amax.cpu()
+                iq.reset_amax()
+                iq.axis = None
+                iq.amax = act_amax.amax()
+            iq.enable()
+        if h.is_enabled:
+            losses = h.loss_acc.tolist()  # the one host read per linear
+            h.loss = dict(zip(h.alphas, (float(torch.tensor(v, dtype=torch.float32)) for v in losses)))
+            h.best_alpha = min(h.loss, key=h.loss.get)
+            h.best_scale = _awq_get_scale(h.act_scale, h.weight_scale, h.best_alpha)
+            apply_pre_quant_scale_and_smooth(module, 1.0 / h.best_scale)
+        else:
+            warnings.warn(f"awq_lite: Forcing pre_quant_scale=1 for {name} because it was not properly exercised "
+                          "during calibration; quantizing with max calibration.")
+            max_calibrate(module, lambda m: m.weight_quantizer(m.weight), distributed_sync=False)
+            iq._enable_pre_quant_scale = True
+            iq.pre_quant_scale = torch.ones(module.weight.shape[1], dtype=module.weight.dtype,
+                                            device=module.weight.device)
+        h.cleanup()
+        if not debug:
+            delattr(module, "awq_lite")
+
+
+@torch.no_grad()
+def awq(model: nn.Module, forward_loop=None, algorithm: str = "awq_lite", **kwargs):
+    """model_calib.py:1362-1391 (awq_clip is not on this path)."""
+    if algorithm not in ("awq_lite",):
+        raise NotImplementedError(f"modelopt_b200: AWQ algorithm {algorithm!r} is not implemented (awq_lite only)")
+    with SequentialQuantizer.convert_to_single_quantizer(model):
+        awq_lite(model, forward_loop, **kwargs)
+    from .utils import is_quantized_linear
+
+    for module in model.modules():
+        if is_quantized_linear(module) and isinstance(module.weight_quantizer, SequentialQuantizer):
+            max_calibrate(module, lambda lin: lin.weight_quantizer(lin.weight), distributed_sync=False)
+
+
+__all__ += ["awq_lite", "awq", "AWQLiteHelper"]

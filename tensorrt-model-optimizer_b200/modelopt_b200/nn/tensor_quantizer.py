@@ -574,7 +574,10 @@ class TensorQuantizer(nn.Module):
         if inputs.numel() == 0:
             return inputs
         if self.pre_quant_scale is not None:
-            inputs = inputs * self.pre_quant_scale
+            fused = self._forward_fused_pre_quant_scale(inputs)
+            if fused is not None:
+                return fused
+            inputs = self._apply_pre_quant_scale(inputs)
         if self._disabled:
             self._input_dtype = inputs.dtype if hasattr(inputs, "dtype") else None
             return inputs
@@ -601,6 +604,59 @@ class TensorQuantizer(nn.Module):
         if self.is_static_block_quant:
             outputs = self._reset_to_original_shape(outputs)
         return outputs
+
+    def _apply_pre_quant_scale(self, inputs):
+        """inputs * pre_quant_scale (tensor_quantizer.py:1143); one mo_scale_cols_amax launch when no gradient is
+        needed and the scale is a last-dim vector of the input dtype."""
+        pqs = self._pre_quant_scale
+        if (inputs.is_cuda and not (torch.is_grad_enabled() and (inputs.requires_grad or pqs.requires_grad))
+                and pqs.dtype == inputs.dtype and pqs.numel() == inputs.shape[-1] and pqs.numel() > 1
+                and inputs.dtype in (torch.float32, torch.float16, torch.bfloat16)):
+            from .. import ops
+
+            return ops.scale_cols(inputs.contiguous(), pqs)
+        return inputs * pqs
+
+    def _forward_fused_pre_quant_scale(self, inputs):
+        """`inputs * pre_quant_scale` folded into the fake-quant kernel (one pass instead of two, row a5): taken when
+        no gradient is needed and the format is INT-N / FP8 with a stored amax, or INT-N over last-dim blocks (stored
+        or per-call amax).  Returns None when the general path must run."""
+        from .. import ops
+
+        pqs = self._pre_quant_scale
+        if (self._disabled or not self._if_quant or self._if_calib or not self._fake_quant or self.backend is not None
+                or not inputs.is_cuda or (torch.is_grad_enabled() and inputs.requires_grad)
+                or pqs.dtype != inputs.dtype or pqs.numel() != inputs.shape[-1] or inputs.dtype == torch.float64
+                or self._use_constant_amax or self._dynamic or getattr(self, "_bias", None) is not None):
+            return None
+        bs = self.block_sizes
+        is_int = isinstance(self._num_bits, int)
+        if bs is None:
+            if not hasattr(self, "_amax"):
+                return None
+            amax = self._get_amax(inputs)
+            try:
+                if is_int:
+                    return ops.qdq_int(inputs, amax, self._num_bits, self._unsigned, self._narrow_range, prescale=pqs)
+                if self._num_bits == (4, 3):
+                    return ops.qdq_fp8(inputs, amax, prescale=pqs)
+            except ValueError:  # amax is not a scalar / single-axis vector
+                return None
+            return None
+        keys = {k for k in bs if isinstance(k, int)}
+        block = bs.get(-1) or bs.get(inputs.dim() - 1)
+        if (not is_int or bs.get("type", "static") != "static" or len(keys) != 1 or not block
+                or inputs.shape[-1] % block != 0):
+            return None
+        x = inputs.contiguous()
+        if hasattr(self, "_amax"):
+            amax = self._get_amax(inputs)
+            if amax.numel() != x.numel() // block:
+                return None
+            y = ops.qdq_int(x.view(-1, block), amax.reshape(-1, 1), self._num_bits, self._unsigned,
+                            self._narrow_range, prescale=pqs)
+            return y.view(inputs.shape)
+        return ops.qdq_int_block_dynamic(x, block, self._num_bits, self._unsigned, self._narrow_range, prescale=pqs)
 
     # ------------------------------------------------------------------ repr / state
     def _short_amax(self, fmt=".2e"):

@@ -135,26 +135,41 @@ def _via_f32(fn, x, *a, **k):
 
 
 # ------------------------------------------------------------------------------------------------
-def qdq_int(x, amax, num_bits=8, unsigned=False, narrow_range=True, out=None, status=None):
+def _prescale_vec(prescale, x):
+    """pre_quant_scale as the fp32 copy of its x.dtype values, [x.shape[-1]] (None passes through)."""
+    if prescale is None:
+        return None, 1
+    cols = prescale.numel()
+    if cols == 0 or x.numel() % cols != 0 or (x.shape[-1] % cols != 0 and cols % x.shape[-1] != 0):
+        raise ValueError(f"prescale has {cols} elements, which does not tile the rows of a {tuple(x.shape)} tensor")
+    return _f32_vec(prescale.to(x.dtype), x), cols
+
+
+def qdq_int(x, amax, num_bits=8, unsigned=False, narrow_range=True, out=None, status=None, prescale=None):
+    """`prescale` (optional, x.shape[-1] values): quantize (x * prescale) rounded to x.dtype, in the same pass."""
     _cuda(x, "qdq_int")
     if x.dtype == torch.float64:
-        return _via_f32(qdq_int, x, amax, num_bits, unsigned, narrow_range, None, status)
+        return _via_f32(qdq_int, x, amax, num_bits, unsigned, narrow_range, None, status, prescale)
     x = x.contiguous()
     axis_size, inner = _axis_of(x, amax)
     am = _f32_vec(amax, x)
+    ps, cols = _prescale_vec(prescale, x)
     y = torch.empty_like(x) if out is None else out
     with _dev(x):
-        _launched(_lib.load().mo_qdq_int(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), am.data_ptr(), axis_size,
-                                     inner, int(num_bits), int(bool(unsigned)), int(bool(narrow_range)),
-                                     status.data_ptr() if status is not None else None, _stream(x)), "mo_qdq_int")
+        _launched(_lib.load().mo_qdq_int_pqs(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), am.data_ptr(), axis_size,
+                                             inner, int(num_bits), int(bool(unsigned)), int(bool(narrow_range)),
+                                             status.data_ptr() if status is not None else None,
+                                             ps.data_ptr() if ps is not None else None, cols, _stream(x)),
+                  "mo_qdq_int")
     return y
 
 
-def qdq_fp8(x, amax=None, out=None, numerics=None):
+def qdq_fp8(x, amax=None, out=None, numerics=None, prescale=None):
     _cuda(x, "qdq_fp8")
     if x.dtype == torch.float64:
-        return _via_f32(qdq_fp8, x, amax, None, numerics)
+        return _via_f32(qdq_fp8, x, amax, None, numerics, prescale)
     x = x.contiguous()
+    ps, cols = _prescale_vec(prescale, x)
     y = torch.empty_like(x) if out is None else out
     if amax is None:
         axis_size, inner, ap, am = 1, x.numel(), None, None
@@ -163,8 +178,9 @@ def qdq_fp8(x, amax=None, out=None, numerics=None):
         am = _f32_vec(amax, x)
         ap = am.data_ptr()
     with _dev(x):
-        _launched(_lib.load().mo_qdq_fp8(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), ap, axis_size, inner,
-                                     _mode(numerics), _stream(x)), "mo_qdq_fp8")
+        _launched(_lib.load().mo_qdq_fp8_pqs(x.data_ptr(), y.data_ptr(), x.numel(), _code(x), ap, axis_size, inner,
+                                             _mode(numerics), ps.data_ptr() if ps is not None else None, cols,
+                                             _stream(x)), "mo_qdq_fp8")
     return y
 
 
@@ -514,3 +530,112 @@ def mse_sweep_into(x, cand_amax, losses, num_bits=8, unsigned=False, narrow_rang
                                            8 if fp8 else int(num_bits), int(bool(unsigned)),
                                            int(bool(narrow_range)), int(fp8), _mode(numerics), losses.data_ptr(),
                                            _stream(x)), "mo_mse_sweep")
+
+
+# ------------------------------------------------------------------------------------------------
+# SmoothQuant / AWQ-lite support (csrc/smooth.cu, csrc/qdq_ew.cu)
+# ------------------------------------------------------------------------------------------------
+def qdq_int_block_dynamic(x, block, num_bits=4, unsigned=False, narrow_range=False, prescale=None, out=None,
+                          return_amax=False):
+    """INT-N fake quant with the amax of each `block` consecutive last-dim elements taken from the data, after an
+    optional per-column `prescale` multiply (a tensor of x.shape[-1] values, rounded like `x * prescale` in x.dtype).
+    ONE pass.  Returns y (and the fp32 [n_blocks] amax when asked)."""
+    _cuda(x, "qdq_int_block_dynamic")
+    x = x.contiguous()
+    cols = x.shape[-1]
+    if cols % block != 0:
+        raise ValueError(f"last dim {cols} is not a multiple of block {block}")
+    y = torch.empty_like(x) if out is None else out
+    assert y.is_contiguous() and y.shape == x.shape and y.dtype == x.dtype
+    nb = x.numel() // block
+    ps = None
+    if prescale is not None:
+        if prescale.numel() != cols:
+            raise ValueError(f"prescale has {prescale.numel()} elements, last dim is {cols}")
+        ps = _f32_vec(prescale.to(x.dtype), x)
+    am = torch.empty(nb, dtype=torch.float32, device=x.device) if return_amax else None
+    with _dev(x):
+        _launched(_lib.load().mo_qdq_int_block_dynamic(x.data_ptr(), y.data_ptr(), nb, block, _code(x),
+                                                       ps.data_ptr() if ps is not None else None, cols,
+                                                       int(num_bits), int(bool(unsigned)), int(bool(narrow_range)),
+                                                       am.data_ptr() if am is not None else None, _stream(x)),
+                  "mo_qdq_int_block_dynamic")
+    return (y, am) if return_amax else y
+
+
+def scale_cols(x, scale, out=None, amax_bits=None, amax_mode="none"):
+    """out = (x * scale[None, :]) rounded to x.dtype over the [-1, x.shape[-1]] view (out may be x); optionally the
+    amax of the result in the same pass, merged into `amax_bits` (int32 bit patterns: [1] 'tensor' or [rows] 'row')."""
+    _cuda(x, "scale_cols")
+    assert x.is_contiguous()
+    cols = x.shape[-1]
+    rows = x.numel() // cols if cols else 0
+    y = torch.empty_like(x) if out is None else out
+    assert y.is_contiguous() and y.shape == x.shape and y.dtype == x.dtype
+    s = _f32_vec(scale, x)
+    if s.numel() != cols:
+        raise ValueError(f"scale has {s.numel()} elements, last dim is {cols}")
+    mode = {"none": 0, "tensor": 1, "row": 2}[amax_mode]
+    if mode:
+        assert amax_bits is not None and amax_bits.dtype == torch.int32 and amax_bits.is_contiguous()
+        assert amax_bits.numel() == (1 if mode == 1 else rows)
+    with _dev(x):
+        _launched(_lib.load().mo_scale_cols_amax(x.data_ptr(), y.data_ptr(), rows, cols, _code(x), s.data_ptr(),
+                                                 amax_bits.data_ptr() if mode else None, mode, _stream(x)),
+                  "mo_scale_cols_amax")
+    return y
+
+
+def _round_like(v32: torch.Tensor, dtype) -> torch.Tensor:
+    return v32.to(dtype).to(torch.float32)
+
+
+def _col_splits(rows: int, cols: int, per_vec: int) -> int:
+    strips = max(1, -(-cols // (32 * per_vec)))
+    return int(max(1, min(-(-rows // 8), -(-4 * 148 // strips), 512)))
+
+
+def awq_weight_scale(weight, block_size=None):
+    """AWQ get_weight_scale (model_calib.py:1453-1469): mean over rows of |w| / (blockmax + tiny), fp32 [cols]."""
+    _cuda(weight, "awq_weight_scale")
+    w = weight.contiguous().reshape(-1, weight.shape[-1])
+    rows, cols = w.shape
+    block = int(block_size) if block_size else cols
+    per_vec = 8 if w.dtype == torch.float32 else 16
+    splits = _col_splits(rows, cols, per_vec)
+    partial = torch.empty(splits, cols, dtype=torch.float32, device=w.device)
+    with _dev(w):
+        _launched(_lib.load().mo_awq_weight_scale(w.data_ptr(), rows, cols, _code(w), block, partial.data_ptr(),
+                                                  splits, _stream(w)), "mo_awq_weight_scale")
+    return _round_like(partial.sum(0) / rows, w.dtype)
+
+
+def abs_col_sum(x):
+    """sum over rows of |x| per last-dim column, fp32 [cols] (AWQ get_act_scale numerator)."""
+    _cuda(x, "abs_col_sum")
+    x2 = x.contiguous().reshape(-1, x.shape[-1])
+    rows, cols = x2.shape
+    per_vec = 8 if x2.dtype == torch.float32 else 16
+    splits = _col_splits(rows, cols, per_vec)
+    partial = torch.empty(splits, cols, dtype=torch.float32, device=x2.device)
+    with _dev(x2):
+        _launched(_lib.load().mo_abs_col_sum(x2.data_ptr(), rows, cols, _code(x2), partial.data_ptr(), splits,
+                                             _stream(x2)), "mo_abs_col_sum")
+    return partial.sum(0)
+
+
+def awq_act_scale(x):
+    """AWQ get_act_scale (model_calib.py:1471-1472): x.abs().view(-1, C).mean(0).to(float32)."""
+    rows = x.numel() // x.shape[-1]
+    return _round_like(abs_col_sum(x) / rows, x.dtype)
+
+
+def sq_diff_mean_into(a, b, acc):
+    """acc (float64 scalar tensor on the device) += mean((a - b)^2), the difference rounded to a.dtype first."""
+    _cuda(a, "sq_diff_mean_into")
+    assert a.shape == b.shape and a.dtype == b.dtype and acc.dtype == torch.float64 and acc.numel() == 1
+    a, b = a.contiguous(), b.contiguous()
+    with _dev(a):
+        _launched(_lib.load().mo_sq_diff_mean(a.data_ptr(), b.data_ptr(), a.numel(), _code(a), acc.data_ptr(),
+                                              _stream(a)), "mo_sq_diff_mean")
+    return acc
