@@ -85,7 +85,7 @@ def test_qdq_with_prescale(dn):
 
 @pytest.mark.parametrize("dn", list(DTYPES))
 def test_awq_scales(dn):
-    from modelopt_b200 import ops
+    from modelopt_b200 import model_calib, ops
 
     torch.manual_seed(11)
     dt = DTYPES[dn]
@@ -94,7 +94,7 @@ def test_awq_scales(dn):
     x = (torch.randn(5, 77, 512) * 3).to(dt)
     tol = dict(rtol=2e-6, atol=0) if dt == torch.float32 else dict(rtol=2.0 ** -7, atol=0)
     for block in (128, 16, 512, None):
-        got = ops.awq_weight_scale(w.cuda(), block).cpu()
+        got = model_calib._awq_weight_scale(w.cuda(), block).cpu()  # one kernel when the block fits a warp
         want = osm.awq_weight_scale(w, block)
         torch.testing.assert_close(got, want, **tol)
         assert (got != want).float().mean() <= (0.5 if dt == torch.float32 else 0.02)
@@ -110,6 +110,7 @@ def test_awq_scales(dn):
 
 def test_tensor_quantizer_fused_pre_quant_scale_equals_two_pass():
     from modelopt_b200 import ops
+    from modelopt_b200.config import QuantizerAttributeConfig
     from modelopt_b200.nn import TensorQuantizer
 
     torch.manual_seed(2)
@@ -118,7 +119,7 @@ def test_tensor_quantizer_fused_pre_quant_scale_equals_two_pass():
     cfgs = [({"num_bits": 8, "axis": None}, True), ({"num_bits": (4, 3), "axis": None}, True),
             ({"num_bits": 4, "block_sizes": {-1: 128}}, False), ({"num_bits": 4, "block_sizes": {-1: 128}}, True)]
     for cfg, with_amax in cfgs:
-        q = TensorQuantizer(cfg).cuda()
+        q = TensorQuantizer(QuantizerAttributeConfig(**cfg)).cuda()
         q._enable_pre_quant_scale = True
         q.pre_quant_scale = pqs
         if with_amax:
