@@ -220,6 +220,18 @@ int mo_abs_col_sum(const void* x, int64_t rows, int64_t cols, int dtype, float* 
 int mo_sq_diff_mean(const void* a, const void* b, int64_t n, int dtype, double* acc, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Quant-aware linear (row a15): hand-written tcgen05 GEMM, fp32 accumulation in TMEM.
+ * ---------------------------------------------------------------------------------------------- */
+/* out[M,N] = T(x[M,K] . w[N,K]^T + bias[N]) with x, w, bias, out of `dtype` (MO_BF16 / MO_F16), row-major.
+ * Replaces the F.linear inside QuantLinearConvBase.forward / _QuantLinear.quantized_linear_fn
+ * (nn/modules/quant_module.py:192-278, quant_linear.py:38-53); x and w are the fake-quantized operands.
+ * Loss mode (ref != NULL): nothing is stored, loss_acc[0] += mean((T(out) - ref)^2) (fp64 device accumulator) -
+ * the GEMM + update_loss pair of the AWQ-lite search (model_calib.py:1537-1551, :1485-1491).
+ * K and N must be multiples of 8, pointers 16-byte aligned; bias may be NULL. */
+int mo_linear(const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K, int dtype,
+              const void* ref, double* loss_acc, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.
  * ---------------------------------------------------------------------------------------------- */

@@ -1,0 +1,354 @@
+// Quant-aware linear: out[M,N] = xq[M,K] . wq[N,K]^T (+ bias), bf16/f16 operands, fp32 accumulation in TMEM.
+//
+// Replaces the F.linear of QuantLinearConvBase.forward / _QuantLinear.quantized_linear_fn (reference
+// nn/modules/quant_module.py:192-278, quant_linear.py:38-53) and the 11 GEMMs + loss reductions AWQ-lite runs per
+// linear per batch (model_calib.py:1537-1551, :1485-1491): in loss mode the epilogue accumulates
+// mean((T(out) - ref)^2) and never writes `out`.
+//
+// Shape of the kernel (sm_100a, hand-written tcgen05):
+//   * persistent grid, one CTA per SM, 192 threads: warp 0 = TMA producer, warp 1 = tcgen05.mma issuer (one elected
+//     lane) and TMEM owner, warps 2..5 = epilogue (each reads its own 32-lane quarter of TMEM);
+//   * CTA tile 128 x 256, K step 64 (one 128-byte swizzle row of bf16), 4-stage smem ring (4 x 48 KB) filled by
+//     cp.async.bulk.tensor (SWIZZLE_128B) and released by tcgen05.commit;
+//   * two 256-column fp32 accumulators in TMEM (all 512 columns): the epilogue of tile i overlaps the MMAs of tile i+1;
+//   * tiles are walked in groups of 16 M-blocks x all N-blocks so that the group's activation rows and the whole
+//     weight stay L2-resident.
+// K must be a multiple of 8 and N a multiple of 8 (16-byte TMA strides / vector stores); M is arbitrary (TMA zero-
+// fills out-of-range rows, the epilogue masks them).
+#include <cuda.h>  // CUtensorMap types only: the encode entry point is fetched from the driver at run time
+
+#include <type_traits>
+
+#include "common.cuh"
+
+namespace mo {
+
+constexpr int BM = 128, BN = 256, BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int kStages = 4;
+constexpr int kGemmThreads = 192;
+constexpr uint32_t kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
+constexpr int kGroupM = 16;
+
+struct GemmSmem {
+  uint8_t a[kStages][kABytes];
+  uint8_t b[kStages][kBBytes];
+  uint64_t full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug traps (the launch fails with an error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try(bar, parity)) {
+    if (++spins > (1u << 22)) __trap();
+  }
+}
+
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+// K-major operand tile in the SWIZZLE_128B canonical layout: rows of 128 bytes, 8-row groups 1024 bytes apart.
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);   // start address >> 4            bits [0,14)
+  d |= (uint64_t)1 << 16;                     // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024u >> 4) << 32;          // stride byte offset >> 4       bits [32,46)
+  d |= (uint64_t)1 << 46;                     // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;                     // SWIZZLE_128B
+  return d;
+}
+
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                         uint32_t accumulate) {
+  asm volatile(
+      "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,"
+      "%29,%30,%31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+struct TileCoord {
+  int m_blk, n_blk;
+};
+__device__ __forceinline__ TileCoord tile_coord(int tile, int tiles_m, int tiles_n) {
+  const int per_group = kGroupM * tiles_n;
+  const int g = tile / per_group, r = tile - g * per_group;
+  const int gm = min(kGroupM, tiles_m - g * kGroupM);
+  TileCoord c;
+  c.n_blk = r / gm;
+  c.m_blk = g * kGroupM + (r - c.n_blk * gm);
+  return c;
+}
+
+// kHalf: operands / output are f16 (else bf16).  kLoss: accumulate the squared error against `ref`, no store.
+template <bool kHalf, bool kLoss>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+linear_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                      const void* __restrict__ bias_v, void* __restrict__ out_v, const void* __restrict__ ref_v,
+                      double* __restrict__ loss_acc, double loss_scale, int M, int N, int K) {
+  using T = typename std::conditional<kHalf, __half, __nv_bfloat16>::type;
+  extern __shared__ uint8_t smem_raw[];
+  GemmSmem& s = *reinterpret_cast<GemmSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN, num_tiles = tiles_m * tiles_n;
+  const int num_kb = (K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&s.tmem_full[i], 1); mbar_init(&s.tmem_empty[i], 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s.tmem_base;
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const TileCoord tc = tile_coord(tile, tiles_m, tiles_n);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&s.empty[stage], phase ^ 1);
+          mbar_expect_tx(&s.full[stage], kStageBytes);
+          tma_load_2d(s.a[stage], &map_a, &s.full[stage], kb * BK, tc.m_blk * BM);
+          tma_load_2d(s.b[stage], &map_b, &s.full[stage], kb * BK, tc.n_blk * BN);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      // instruction descriptor: D = F32, A/B = BF16 (1) or F16 (0), both K-major, N >> 3 at [17,23), M >> 4 at [24,29)
+      const uint32_t fmt = kHalf ? 0u : 1u;
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&s.tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&s.full[stage], phase);
+          tc_fence_after();
+          const uint64_t da = umma_desc(smem_u32(s.a[stage])), db = umma_desc(smem_u32(s.b[stage]));
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            // +32 bytes per UMMA_K step inside the 128-byte swizzle row: +2 in the (>>4) address field
+            umma_f16(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+          }
+          umma_commit(&s.empty[stage]);          // smem slot is free once these MMAs have read it
+          if (kb == num_kb - 1) umma_commit(&s.tmem_full[acc]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===== epilogue: warps 2..5 own TMEM lanes 32*(warp%4) .. +31 =====
+    const int quarter = warp & 3;
+    const T* bias = static_cast<const T*>(bias_v);
+    T* out = static_cast<T*>(out_v);
+    const T* ref = static_cast<const T*>(ref_v);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    float loss = 0.f;
+    double dloss = 0.0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const TileCoord tc = tile_coord(tile, tiles_m, tiles_n);
+      mbar_wait(&s.tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = tc.m_blk * BM + quarter * 32 + lane;
+      const int n0 = tc.n_blk * BN;
+      const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(taddr + (uint32_t)c0, r);   // warp-collective: every lane takes part even when its row is masked
+        if (row < M) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const int col = n0 + c0 + j;
+            if (col < N) {
+              float f[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
+              if (bias != nullptr) {
+                const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
+                const T* bp = reinterpret_cast<const T*>(&bv);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = __fadd_rn(f[i], Elem<T>::load(bp + i));
+              }
+              uint4 o;
+              T* op = reinterpret_cast<T*>(&o);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) Elem<T>::store(op + i, f[i]);
+              if constexpr (kLoss) {
+                const uint4 rv = __ldg(reinterpret_cast<const uint4*>(ref + (int64_t)row * N + col));
+                const T* rp = reinterpret_cast<const T*>(&rv);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  T dt;
+                  Elem<T>::store(&dt, __fsub_rn(Elem<T>::load(op + i), Elem<T>::load(rp + i)));
+                  const float d = Elem<T>::load(&dt);
+                  loss = __fmaf_rn(d, d, loss);
+                }
+              } else {
+                *reinterpret_cast<uint4*>(out + (int64_t)row * N + col) = o;
+              }
+            }
+          }
+        }
+      }
+      if constexpr (kLoss) { dloss += (double)loss; loss = 0.f; }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s.tmem_empty[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if constexpr (kLoss) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dloss += __shfl_xor_sync(0xffffffffu, dloss, o);
+      if (lane == 0 && dloss != 0.0) atomicAdd(loss_acc, dloss * loss_scale);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Host side
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// [rows, K] row-major 16-bit matrix, box = [box_rows, 64] with the 128-byte swizzle.
+static bool make_map(CUtensorMap* m, const void* base, int64_t rows, int64_t K, int box_rows, bool half) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return false; }
+  const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(m, half ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return false; }
+  return true;
+}
+
+template <bool kHalf, bool kLoss>
+static int linear_launch(const CUtensorMap& ma, const CUtensorMap& mb, const void* bias, void* out, const void* ref,
+                         double* loss_acc, int M, int N, int K, cudaStream_t s) {
+  auto kern = linear_tcgen05_kernel<kHalf, kLoss>;
+  const int smem = (int)sizeof(GemmSmem) + 1024;
+  static bool configured = false;
+  if (!configured) {
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { set_error("mo_linear: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    configured = true;
+  }
+  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int grid = tiles < kNumSMs ? tiles : kNumSMs;
+  kern<<<grid, kGemmThreads, smem, s>>>(ma, mb, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), M, N, K);
+  return check_launch("mo_linear");
+}
+
+}  // namespace mo
+
+using namespace mo;
+
+extern "C" int mo_linear(const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K,
+                         int dtype, const void* ref, double* loss_acc, void* stream) {
+  if (M < 0 || N < 0 || K < 0) { set_error("mo_linear: bad shape"); return MO_ERR_SHAPE; }
+  if (M == 0 || N == 0) return MO_OK;
+  if (dtype != MO_BF16 && dtype != MO_F16) { set_error("mo_linear: bf16 / f16 only (dtype %d)", dtype); return MO_ERR_DTYPE; }
+  const bool loss = ref != nullptr || loss_acc != nullptr;
+  if (!x || !w || (loss ? (!ref || !loss_acc) : !out)) { set_error("mo_linear: NULL pointer"); return MO_ERR_NULL; }
+  if (K < 8 || K % 8 != 0 || N % 8 != 0) { set_error("mo_linear: K and N must be multiples of 8 (K=%lld N=%lld)", (long long)K, (long long)N); return MO_ERR_SHAPE; }
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) { set_error("mo_linear: dimension too large"); return MO_ERR_SHAPE; }
+  auto mis = [](const void* p) { return p && (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
+  if (mis(x) || mis(w) || mis(bias) || mis(out) || mis(ref)) { set_error("mo_linear: pointers must be 16-byte aligned"); return MO_ERR_ARG; }
+  const bool half = dtype == MO_F16;
+  CUtensorMap ma, mb;
+  if (!make_map(&ma, x, M, K, BM, half) || !make_map(&mb, w, N, K, BN, half)) return MO_ERR_ARG;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int m = (int)M, n = (int)N, k = (int)K;
+  if (half) return loss ? linear_launch<true, true>(ma, mb, bias, out, ref, loss_acc, m, n, k, s)
+                        : linear_launch<true, false>(ma, mb, bias, out, ref, loss_acc, m, n, k, s);
+  return loss ? linear_launch<false, true>(ma, mb, bias, out, ref, loss_acc, m, n, k, s)
+              : linear_launch<false, false>(ma, mb, bias, out, ref, loss_acc, m, n, k, s);
+}

@@ -639,3 +639,54 @@ def sq_diff_mean_into(a, b, acc):
         _launched(_lib.load().mo_sq_diff_mean(a.data_ptr(), b.data_ptr(), a.numel(), _code(a), acc.data_ptr(),
                                               _stream(a)), "mo_sq_diff_mean")
     return acc
+
+
+# ------------------------------------------------------------------------------------------------
+# Quant-aware linear (csrc/gemm.cu): tcgen05 GEMM
+# ------------------------------------------------------------------------------------------------
+def linear_supported(x, weight, bias=None) -> bool:
+    """Shapes / dtypes the tcgen05 kernel takes (bf16 or f16, K and N multiples of 8, 16-byte aligned rows)."""
+    if not (x.is_cuda and weight.is_cuda and x.dtype == weight.dtype and x.dtype in (torch.bfloat16, torch.float16)
+            and weight.dim() == 2 and x.dim() >= 1 and x.shape[-1] == weight.shape[1]):
+        return False
+    N, K = weight.shape
+    if K < 8 or K % 8 or N % 8 or (bias is not None and (bias.dtype != x.dtype or bias.numel() != N)):
+        return False
+    return True
+
+
+def linear(x, weight, bias=None, out=None):
+    """x[..., K] @ weight[N, K]^T (+ bias) -> [..., N]; fp32 accumulation in TMEM, output in x.dtype."""
+    _cuda(x, "linear")
+    if not linear_supported(x, weight, bias):
+        raise ValueError(f"modelopt_b200.linear: unsupported operands x={tuple(x.shape)} {x.dtype}, "
+                         f"weight={tuple(weight.shape)} {weight.dtype} (bf16/f16, K and N multiples of 8)")
+    x2 = x.contiguous().reshape(-1, x.shape[-1])
+    w = weight.contiguous()
+    b = bias.contiguous() if bias is not None else None
+    M, K = x2.shape
+    N = w.shape[0]
+    y = torch.empty(*x.shape[:-1], N, dtype=x.dtype, device=x.device) if out is None else out
+    assert y.is_contiguous() and y.numel() == M * N and y.dtype == x.dtype
+    with _dev(x):
+        _launched(_lib.load().mo_linear(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None,
+                                        y.data_ptr(), M, N, K, _code(x2), None, None, _stream(x)), "mo_linear")
+    return y
+
+
+def linear_loss_into(x, weight, bias, ref, acc):
+    """acc (float64 device scalar) += mean((linear(x, weight, bias) - ref)^2) without writing the output."""
+    _cuda(x, "linear_loss_into")
+    if not linear_supported(x, weight, bias):
+        raise ValueError("modelopt_b200.linear_loss_into: unsupported operands")
+    x2 = x.contiguous().reshape(-1, x.shape[-1])
+    w = weight.contiguous()
+    b = bias.contiguous() if bias is not None else None
+    r = ref.contiguous()
+    M, K = x2.shape
+    N = w.shape[0]
+    assert r.numel() == M * N and r.dtype == x.dtype and acc.dtype == torch.float64 and acc.numel() == 1
+    with _dev(x):
+        _launched(_lib.load().mo_linear(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None, None,
+                                        M, N, K, _code(x2), r.data_ptr(), acc.data_ptr(), _stream(x)), "mo_linear")
+    return acc
