@@ -475,9 +475,16 @@ def _awq_lite_forward(self, input, *args, **kwargs):
     ref = out_actual[0] if isinstance(out_actual, tuple) else out_actual
     self.input_quantizer._enable_pre_quant_scale = True
     self.weight_quantizer._enable_pre_quant_scale = True
+    # bf16 / f16 linears: GEMM and loss in ONE tcgen05 kernel per alpha, the candidate output is never written
+    fused = (hasattr(self, "_tcgen05_ok") and self._tcgen05_ok(input, args, kwargs)
+             and not self.output_quantizer.is_enabled and ref.dtype == input.dtype and not isinstance(out_actual, tuple))
     for k, (inv_s, s) in enumerate(h.scales):
         self.input_quantizer.pre_quant_scale = inv_s
         self.weight_quantizer.pre_quant_scale = s
+        if fused:
+            ops.linear_loss_into(self.input_quantizer(input), self.weight_quantizer(self._parameters["weight"]),
+                                 self.bias, ref, h.loss_acc[k:k + 1])
+            continue
         out = self._forward_no_awq(input, *args, **kwargs)
         out = out[0] if isinstance(out, tuple) else out
         if out.is_cuda and out.dtype == ref.dtype and out.dtype != torch.float64:

@@ -283,7 +283,8 @@ class TensorQuantizer(nn.Module):
         else:
             if self._pre_quant_scale.shape != value.shape:
                 raise RuntimeError("Changing shape when setting pre_quant_scale is not allowed.")
-            self._pre_quant_scale.data.copy_(value.clone().detach().to(self._pre_quant_scale.device))
+            with torch.no_grad():  # copy_ on the buffer itself: bumps _version, which the weight cache keys on
+                self._pre_quant_scale.copy_(value.detach().to(self._pre_quant_scale.device))
 
     @property
     def amax(self):
@@ -305,7 +306,8 @@ class TensorQuantizer(nn.Module):
         else:
             if self._amax.shape != value.shape:
                 raise RuntimeError("Changing shape when setting amax is not allowed.")
-            self._amax.data.copy_(value.clone().detach().to(self._amax.device))
+            with torch.no_grad():  # copy_ on the buffer itself: bumps _version, which the weight cache keys on
+                self._amax.copy_(value.detach().to(self._amax.device))
 
     def reset_amax(self):
         if hasattr(self, "_amax"):
@@ -604,6 +606,21 @@ class TensorQuantizer(nn.Module):
         if self.is_static_block_quant:
             outputs = self._reset_to_original_shape(outputs)
         return outputs
+
+    def cache_key(self):
+        """Everything the fake-quantized value of a tensor depends on beside the tensor itself; None when the
+        quantizer is collecting statistics or its result may not be reused."""
+        if self._if_calib or self._dynamic or self.backend is not None:
+            return None
+        bufs = []
+        for name in ("_amax", "_pre_quant_scale", "_global_amax", "_bias_value"):
+            t = getattr(self, name, None)
+            bufs.append(None if t is None else (t.data_ptr(), t._version, tuple(t.shape)))
+        bs = self._block_sizes
+        return (self._disabled, self._if_quant, self._fake_quant, self._num_bits, self._unsigned, self._narrow_range,
+                self._axis if not isinstance(self._axis, list) else tuple(self._axis),
+                None if bs is None else tuple(sorted(((str(k), str(v)) for k, v in bs.items()))),
+                self._enable_pre_quant_scale, self._use_constant_amax, tuple(bufs))
 
     def _apply_pre_quant_scale(self, inputs):
         """inputs * pre_quant_scale (tensor_quantizer.py:1143); one mo_scale_cols_amax launch when no gradient is

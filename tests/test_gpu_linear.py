@@ -1,0 +1,122 @@
+"""GPU parity: the tcgen05 quant-aware linear (through the C ABI) vs a plain PyTorch fp32 reference of the same op
+(tolerance: bf16 / f16 output rounding + fp32 accumulation order, stated per test) and vs cuBLAS on the same operands."""
+
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+from torch import nn
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(128, 256, 64), (128, 256, 256), (256, 512, 128), (1000, 264, 72), (77, 8, 8), (1, 4096, 1024),
+          (300, 520, 4096), (2048, 1024, 2048)]
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("bias", [True, False])
+def test_linear_vs_fp32_reference(M, N, K, dt, bias):
+    from modelopt_b200 import ops
+
+    torch.manual_seed(M * 3 + N * 5 + K)
+    x = torch.randn(M, K, device="cuda", dtype=dt)
+    w = torch.randn(N, K, device="cuda", dtype=dt) * 0.05
+    b = torch.randn(N, device="cuda", dtype=dt) if bias else None
+    y = ops.linear(x, w, b)
+    want = x.float() @ w.float().t() + (b.float() if bias else 0.0)
+    # one output ulp (2^-8 bf16 / 2^-11 f16, relative) + fp32 accumulation-order noise
+    ulp = 2.0 ** -8 if dt == torch.bfloat16 else 2.0 ** -11
+    torch.testing.assert_close(y.float(), want, rtol=ulp, atol=ulp * want.abs().max().item() * 0.25)
+    ref = F.linear(x, w, b)  # cuBLAS, same operands, also fp32 accumulation
+    assert (y != ref).float().mean().item() <= 0.02
+    torch.testing.assert_close(y.float(), ref.float(), rtol=2 * ulp, atol=ulp * want.abs().max().item() * 0.25)
+
+
+def test_linear_batched_input_and_errors():
+    from modelopt_b200 import ops
+
+    x = torch.randn(3, 50, 128, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(64, 128, device="cuda", dtype=torch.bfloat16)
+    y = ops.linear(x, w)
+    assert y.shape == (3, 50, 64)
+    torch.testing.assert_close(y.float(), (x.float() @ w.float().t()), rtol=2.0 ** -7, atol=0.1)
+    with pytest.raises(ValueError):
+        ops.linear(x.float(), w.float())
+    with pytest.raises(ValueError):
+        ops.linear(x[..., :100].contiguous(), w[:, :100].contiguous())  # K % 8 != 0
+    with pytest.raises(RuntimeError):
+        ops.linear(x.cpu(), w.cpu())
+    assert ops.linear(x[:0], w).shape == (0, 50, 64)
+
+
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+def test_linear_fused_loss(dt):
+    from modelopt_b200 import ops
+
+    torch.manual_seed(5)
+    x = torch.randn(700, 512, device="cuda", dtype=dt)
+    w = torch.randn(264, 512, device="cuda", dtype=dt) * 0.05
+    b = torch.randn(264, device="cuda", dtype=dt)
+    ref = (F.linear(x, w, b).float() * 1.02 + 0.01).to(dt)
+    acc = torch.zeros(3, dtype=torch.float64, device="cuda")
+    ops.linear_loss_into(x, w, b, ref, acc[1:2])
+    ops.linear_loss_into(x, w, b, ref, acc[1:2])
+    y = ops.linear(x, w, b)
+    want = 2 * (y - ref).float().pow(2).double().mean().item()
+    assert acc[0].item() == 0 and acc[2].item() == 0
+    assert abs(acc[1].item() - want) <= 1e-9 * want + 1e-300
+
+
+def _quant_linear(cfg_name, dt=torch.bfloat16):
+    import modelopt_b200 as mtq
+
+    torch.manual_seed(3)
+    m = nn.Sequential(nn.Linear(512, 1024), nn.GELU(), nn.Linear(1024, 256, bias=False)).to("cuda", dt)
+    data = [torch.randn(4, 64, 512, device="cuda", dtype=dt) for _ in range(2)]
+    mtq.quantize(m, copy.deepcopy(getattr(mtq, cfg_name)), lambda model: [model(b) for b in data])
+    return m, data
+
+
+@pytest.mark.parametrize("cfg", ["INT8_DEFAULT_CFG", "FP8_DEFAULT_CFG", "NVFP4_DEFAULT_CFG",
+                                 "INT4_BLOCKWISE_WEIGHT_ONLY_CFG"])
+def test_quant_linear_forward_matches_three_pass_path(cfg):
+    """no_grad forward (tcgen05, cached weight) vs the reference's structure (QDQ x, QDQ W, F.linear) on the same
+    module: the operands are bit-identical, the GEMMs differ by fp32 accumulation order only."""
+    from modelopt_b200 import ops
+
+    m, data = _quant_linear(cfg)
+    x = data[0]
+    with torch.no_grad():
+        n0 = ops.LAUNCHES[0]
+        y1 = m(x)
+        first = ops.LAUNCHES[0] - n0
+        n0 = ops.LAUNCHES[0]
+        y2 = m(x)
+        second = ops.LAUNCHES[0] - n0
+    assert torch.equal(y1, y2)
+    assert second < first, (first, second)  # the weights were not re-quantized
+    yg = m(x.clone().requires_grad_(True)).detach()  # gradient needed -> cuBLAS path, weights re-quantized
+    assert (y1 != yg).float().mean().item() <= 0.02
+    torch.testing.assert_close(y1.float(), yg.float(), rtol=2.0 ** -6, atol=2.0 ** -6 * yg.float().abs().max().item())
+
+
+def test_quantized_weight_cache_invalidation():
+    m, data = _quant_linear("INT8_DEFAULT_CFG")
+    lin = m[0]
+    x = data[0]
+    with torch.no_grad():
+        y0 = m(x)
+        w_cached = lin.__dict__["_wq_cache"][1]
+        lin.weight_quantizer.amax = lin.weight_quantizer.amax * 0.5   # setter -> buffer version changes
+        y1 = m(x)
+        assert lin.__dict__["_wq_cache"][1] is not w_cached and not torch.equal(y0, y1)
+        w_cached = lin.__dict__["_wq_cache"][1]
+        lin.weight.mul_(1.5)                                          # in-place weight update
+        y2 = m(x)
+        assert lin.__dict__["_wq_cache"][1] is not w_cached and not torch.equal(y1, y2)
+        lin.weight_quantizer.disable()
+        y3 = m(x)
+        want = F.linear(lin.input_quantizer(x), lin.weight, lin.bias)
+        torch.testing.assert_close(m[2](m[1](want)).float(), y3.float(), rtol=2.0 ** -6, atol=1e-2)
