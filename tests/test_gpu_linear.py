@@ -66,7 +66,7 @@ def test_linear_fused_loss(dt):
     y = ops.linear(x, w, b)
     want = 2 * (y - ref).float().pow(2).double().mean().item()
     assert acc[0].item() == 0 and acc[2].item() == 0
-    assert abs(acc[1].item() - want) <= 1e-9 * want + 1e-300
+    assert abs(acc[1].item() - want) <= 1e-6 * want  # fp32 per-thread partial sums
 
 
 def _quant_linear(cfg_name, dt=torch.bfloat16):
