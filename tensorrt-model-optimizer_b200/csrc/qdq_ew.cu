@@ -18,15 +18,35 @@ constexpr int kUnroll = 2;
 // How amax is indexed.
 enum AxisMode { kPerTensor = 0, kPerChunk = 1, kPerElem = 2 };
 
+// n / d for every 32-bit n with one mul.hi and two shifts (Granlund-Montgomery round-up form); d >= 1.
+struct FastDiv {
+  uint32_t d, mul, shift;  // shift = ceil(log2 d) - 1; d == 1 is handled apart
+  __host__ void init(uint32_t d_) {
+    d = d_;
+    uint32_t l = 0;
+    while ((uint64_t(1) << l) < d_) ++l;
+    mul = (uint32_t)(((uint64_t(1) << 32) * ((uint64_t(1) << l) - d_)) / d_ + 1);
+    shift = l == 0 ? 0 : l - 1;
+  }
+  __device__ __forceinline__ uint32_t div(uint32_t n) const {
+    if (d == 1) return n;
+    const uint32_t t = __umulhi(n, mul);
+    return (t + ((n - t) >> 1)) >> shift;
+  }
+};
+
 struct AxisArgs {
   const float* amax;
   int64_t axis_size;
   int64_t inner;
   int mode;
+  bool small;  // n, inner and axis_size all fit 32 bits: FastDiv path
+  FastDiv div_inner, div_axis;
   // channel of element idx
   __device__ __forceinline__ int64_t channel(int64_t idx) const {
-    if (idx < (int64_t(1) << 32) && inner < (int64_t(1) << 32) && axis_size < (int64_t(1) << 32)) {
-      return (uint32_t)((uint32_t)idx / (uint32_t)inner) % (uint32_t)axis_size;
+    if (small) {
+      const uint32_t row = div_inner.div((uint32_t)idx);
+      return row - div_axis.div(row) * (uint32_t)axis_size;
     }
     return (idx / inner) % axis_size;
   }
@@ -175,10 +195,11 @@ __device__ __forceinline__ float prescaled(const T* x, int64_t i, const float* p
   return v;
 }
 
-template <typename T, typename Op>
+template <typename T, typename Op, bool kPre>
 __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                               int64_t n, Op op, bool vectorized,
-                                                              const float* __restrict__ pre, int64_t cols) {
+                                                              const float* __restrict__ pre_arg, int64_t cols) {
+  const float* pre = kPre ? pre_arg : nullptr;  // compile-time NULL: the plain kernels carry no prescale code
   constexpr int E = Elem<T>::kPerVec;
   op.init();
   if (vectorized) {
@@ -201,7 +222,7 @@ __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restric
         if (c < n_vec) {
           float f[E];
           Elem<T>::unpack(v[u], f);
-          if (pre != nullptr) {  // inputs * pre_quant_scale, a T tensor in the reference (tensor_quantizer.py:1143)
+          if constexpr (kPre) {  // inputs * pre_quant_scale, a T tensor in the reference (tensor_quantizer.py:1143)
             const float* ps = pre + (c * E) % cols;
 #pragma unroll
             for (int i = 0; i < E; i += 4) {
@@ -239,7 +260,10 @@ static int launch_stream(const void* x, void* y, int64_t n, Op op, cudaStream_t 
   int64_t tiles = vec ? (n / E + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll)
                       : (n + kThreads - 1) / kThreads;
   const int grid = persistent_grid(tiles, 8);
-  qdq_stream_kernel<T, Op><<<grid, kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, pre, cols);
+  if (pre != nullptr)
+    qdq_stream_kernel<T, Op, true><<<grid, kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, pre, cols);
+  else
+    qdq_stream_kernel<T, Op, false><<<grid, kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, nullptr, 1);
   return check_launch(what);
 }
 
@@ -354,7 +378,7 @@ static int blockdyn_launch(const void* x, void* y, int64_t n_blocks, int block, 
   op.minb = -(bound + (narrow_range ? 0.f : 1.f));
   op.status = nullptr;
   op.ax.mode = kPerElem;  // scale is set per block by the kernel
-  op.ax.amax = nullptr; op.ax.axis_size = 1; op.ax.inner = 1;
+  op.ax.amax = nullptr; op.ax.axis_size = 1; op.ax.inner = 1; op.ax.small = false;
   const int lanes = block / E;
   const bool vec = aligned32(x) && aligned32(y) && block % E == 0 && lanes >= 1 && lanes <= 32 &&
                    (lanes & (lanes - 1)) == 0 && (pre == nullptr || (cols % E == 0 && (reinterpret_cast<uintptr_t>(pre) & 15u) == 0));
@@ -381,6 +405,8 @@ static int make_axis(AxisArgs& ax, const float* amax, int64_t n, int64_t axis_si
   ax.axis_size = axis_size;
   ax.inner = inner;
   ax.mode = axis_size == 1 ? kPerTensor : (inner % per_vec == 0 ? kPerChunk : kPerElem);
+  ax.small = n < (int64_t(1) << 32) && inner < (int64_t(1) << 32) && axis_size < (int64_t(1) << 32);
+  if (ax.small) { ax.div_inner.init((uint32_t)inner); ax.div_axis.init((uint32_t)axis_size); }
   return MO_OK;
 }
 

@@ -87,6 +87,21 @@ def main():
         cq, sfq = ops.nvfp4_pack(x, 16, sf2)
         report("nvfp4 unpack", 2.5625 * n, lambda: ops.nvfp4_unpack(cq, sfq, sf2, 16, torch.bfloat16))
         del cq, sfq
+        sc = (torch.rand(shape[1], device="cuda") + 0.5)
+        scb = sc.to(torch.bfloat16)
+        y = torch.empty_like(x)
+        report("scale_cols (x * s[col])", 4 * n, lambda: ops.scale_cols(x, sc, out=y))
+        bits = torch.zeros(shape[0], dtype=torch.int32, device="cuda")
+        report("scale_cols + per-row amax (smooth fold)", 4 * n, lambda: ops.scale_cols(x, sc, out=y, amax_bits=bits, amax_mode="row"))
+        report("int4 block-128 dynamic amax + QDQ (one pass)", 4 * n, lambda: ops.qdq_int_block_dynamic(x, 128, 4, out=y))
+        report("  same with pre_quant_scale (AWQ search)", 4 * n, lambda: ops.qdq_int_block_dynamic(x, 128, 4, prescale=scb, out=y))
+        report("int8 per-tensor QDQ with pre_quant_scale", 4 * n, lambda: ops.qdq_int(x, am, 8, False, False, out=y, prescale=scb))
+        report("fp8 per-tensor QDQ with pre_quant_scale", 4 * n, lambda: ops.qdq_fp8(x, am, out=y, prescale=scb))
+        report("awq weight_scale (block 128)", 2 * n, lambda: ops.awq_weight_scale(x, 128))
+        report("awq act_scale (|x| column mean)", 2 * n, lambda: ops.awq_act_scale(x))
+        acc = torch.zeros(1, dtype=torch.float64, device="cuda")
+        report("sq_diff_mean (loss)", 4 * n, lambda: ops.sq_diff_mean_into(x, y, acc))
+        report("REF-style 3-pass: x*s, block amax, qdq", 4 * n, lambda: ops.qdq_int((x * scb).view(-1, 128), ops.reduce_amax((x * scb).view(-1, 128), axis=1).float(), 4, False, False))
         del y
         ref = os.path.join(ROOT, "oracle", "_ref")
         if os.path.isdir(os.path.join(ref, "modelopt")):
