@@ -136,7 +136,8 @@ struct IntOp {
     flags = 0;
     if (ax.mode == kPerTensor) set(__ldg(ax.amax));
   }
-  __device__ __forceinline__ float q1(float x) {
+  template <bool kFast>
+  __device__ __forceinline__ float q1t(float x) {
     if (kUnsigned && x < 0.f) flags |= MO_FLAG_NEGATIVE_IN_UNSIGNED;
     float v = __fmul_rn(x, scale);
     // clamp first (bounds are integers, so clamp and rint commute), NaN kept like the reference's
@@ -145,7 +146,7 @@ struct IntOp {
     // rint for |v| < 2^22: add/subtract 1.5*2^23 (round-half-even in the fp32 adder)
     v = __fsub_rn(__fadd_rn(v, 12582912.0f), 12582912.0f);
     float o;
-    if (dfast) {
+    if constexpr (kFast) {
       const float q0 = __fmul_rn(v, dr);
       const float rem = __fmaf_rn(-db, q0, v);
       o = __fmaf_rn(dr, rem, q0);
@@ -156,6 +157,7 @@ struct IntOp {
     o = __uint_as_float((__float_as_uint(o) & 0x7fffffffu) | (__float_as_uint(x) & 0x80000000u));
     return zero ? 0.0f : o;
   }
+  __device__ __forceinline__ float q1(float x) { return dfast ? q1t<true>(x) : q1t<false>(x); }
   template <int N>
   __device__ __forceinline__ void vec(float* f, int64_t idx0) {
     if (ax.mode == kPerChunk) set(__ldg(ax.amax + ax.channel(idx0)));
@@ -164,8 +166,14 @@ struct IntOp {
       for (int i = 0; i < N; ++i) f[i] = one(f[i], idx0 + i);
       return;
     }
+    // one branch per vector, not per element: the exact-division window test is uniform over the vector
+    if (dfast) {
 #pragma unroll
-    for (int i = 0; i < N; ++i) f[i] = q1(f[i]);
+      for (int i = 0; i < N; ++i) f[i] = q1t<true>(f[i]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < N; ++i) f[i] = q1t<false>(f[i]);
+    }
   }
   __device__ __forceinline__ float one(float v, int64_t idx) {
     if (ax.mode != kPerTensor) set(__ldg(ax.amax + ax.channel(idx)));
@@ -319,8 +327,13 @@ __global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_kernel(const T* __r
       if (live) {
         const float am = __uint_as_float(m);
         op.set(am);
+        if (op.dfast) {
 #pragma unroll
-        for (int i = 0; i < E; ++i) f[i] = op.q1(f[i]);
+          for (int i = 0; i < E; ++i) f[i] = op.template q1t<true>(f[i]);
+        } else {
+#pragma unroll
+          for (int i = 0; i < E; ++i) f[i] = op.template q1t<false>(f[i]);
+        }
         Elem<T>::pack(f, v[u]);
         st_stream(yv + c, v[u]);
         if (amax_out != nullptr && (c & (lanes - 1)) == 0) amax_out[c / lanes] = am;

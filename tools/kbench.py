@@ -41,7 +41,9 @@ def report(name, nbytes, fn):
 
 
 def main():
-    shapes = [(16384, 4096), (16384, 14336)] if len(sys.argv) < 2 else [tuple(map(int, sys.argv[1].split("x")))]
+    no_ref = "--no-ref" in sys.argv
+    argv = [a for a in sys.argv[1:] if not a.startswith("--")]
+    shapes = [(16384, 4096), (16384, 14336)] if not argv else [tuple(map(int, argv[0].split("x")))]
     for shape in shapes:
         x = torch.randn(shape, device="cuda", dtype=torch.bfloat16)
         y = torch.empty_like(x)
@@ -104,7 +106,7 @@ def main():
         report("REF-style 3-pass: x*s, block amax, qdq", 4 * n, lambda: ops.qdq_int((x * scb).view(-1, 128), ops.reduce_amax((x * scb).view(-1, 128), axis=1).float(), 4, False, False))
         del y
         ref = os.path.join(ROOT, "oracle", "_ref")
-        if os.path.isdir(os.path.join(ref, "modelopt")):
+        if os.path.isdir(os.path.join(ref, "modelopt")) and not no_ref:
             sys.path[:0] = [ref, os.path.join(ROOT, "oracle", "ref_shims")]
             try:
                 import modelopt.torch.kernels.quantization.gemm as tk
