@@ -21,7 +21,7 @@ import torch
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 REF = os.environ.get("MODELOPT_REFERENCE", "/root/reference")
-sys.path[:0] = [REF, os.path.join(HERE, "ref_shims")]
+sys.path[:0] = [REF, os.path.join(HERE, "ref_shims"), os.path.dirname(HERE)]
 sys.dont_write_bytecode = True
 warnings.filterwarnings("ignore")
 
@@ -264,6 +264,36 @@ def gen_mse():
     print("mse_cpu.npz", len(g), "arrays")
 
 
+def gen_gpt2():
+    """The reference's mtq.quantize(INT8_DEFAULT_CFG) on GPT-2 small on CPU: every quantizer's amax + a logits slice."""
+    import copy
+
+    import modelopt.torch.quantization as mtq
+
+    from oracle.models import gpt2_model_and_batches
+
+    model, batches = gpt2_model_and_batches()
+    g = {"w_fingerprint": to_np(torch.stack([p.double().abs().sum() for p in model.parameters()]))}
+
+    def loop(m):
+        with torch.no_grad():
+            for b in batches:
+                m(b)
+
+    model = mtq.quantize(model, copy.deepcopy(mtq.INT8_DEFAULT_CFG), loop)
+    n = 0
+    for name, mod in model.named_modules():
+        if isinstance(mod, mtq.nn.TensorQuantizer):
+            g[f"{name}|enabled"] = np.asarray(mod.is_enabled)
+            if hasattr(mod, "_amax"):
+                g[f"{name}|_amax"] = to_np(mod._amax.float())
+                n += 1
+    with torch.no_grad():
+        g["logits"] = to_np(model(batches[0][:1, :64]).logits[0, :, :256])
+    np.savez_compressed(os.path.join(OUT, "gpt2_int8_cpu.npz"), **g)
+    print("gpt2_int8_cpu.npz", len(g), "arrays,", n, "calibrated quantizers")
+
+
 def gen_hist():
     from modelopt.torch.quantization.calib import HistogramCalibrator
 
@@ -301,6 +331,6 @@ def gen_hist():
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack", "hist", "quantize", "mse"]
+    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack", "hist", "quantize", "mse", "gpt2"]
     for w in which:
         globals()["gen_" + w]()

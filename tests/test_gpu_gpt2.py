@@ -1,0 +1,51 @@
+"""GPU parity on BASELINE.json configs[0]: random-init GPT-2 small, mtq.quantize(INT8_DEFAULT_CFG), against what the
+REAL reference produced on CPU for the same seeded model and token batches (tests/golden/gpt2_int8_cpu.npz).
+Weight amax: bit-exact.  Activation amax: the forward runs on a different device (CUDA vs CPU GEMM / LayerNorm / GELU
+rounding), so they agree to 1e-4 relative, the tolerance stated here."""
+
+import copy
+
+import pytest
+import torch
+
+from conftest import load_golden
+from oracle.models import gpt2_model_and_batches
+
+pytestmark = pytest.mark.gpu
+
+
+def test_gpt2_small_int8_default_cfg_vs_reference():
+    import modelopt_b200 as mtq
+    from modelopt_b200.nn import TensorQuantizer
+
+    g = load_golden("gpt2_int8_cpu.npz")
+    model, batches = gpt2_model_and_batches()
+    fp = torch.stack([p.double().abs().sum() for p in model.parameters()])
+    assert torch.equal(fp, torch.from_numpy(g["w_fingerprint"])), "seeded init differs from the golden's model"
+    model = model.cuda()
+    batches = [b.cuda() for b in batches]
+
+    def loop(m):
+        with torch.no_grad():
+            for b in batches:
+                m(b)
+
+    mtq.quantize(model, copy.deepcopy(mtq.INT8_DEFAULT_CFG), loop)
+    want = {k[:-len("|_amax")]: torch.from_numpy(g[k]) for k in g.files if k.endswith("|_amax")}
+    got = {n: m for n, m in model.named_modules() if isinstance(m, TensorQuantizer)}
+    calibrated = {n for n, m in got.items() if hasattr(m, "_amax")}
+    assert calibrated == set(want), (sorted(calibrated ^ set(want))[:10])
+    for n, w in want.items():
+        a = got[n]._amax.float().cpu()
+        assert a.shape == w.shape, n
+        if n.endswith("weight_quantizer"):
+            assert torch.equal(a, w), n
+        else:
+            torch.testing.assert_close(a, w, rtol=1e-4, atol=0, msg=n)
+    for n, m in got.items():
+        key = f"{n}|enabled"
+        if key in g.files:
+            assert bool(g[key]) == m.is_enabled, n
+    with torch.no_grad():
+        logits = model(batches[0][:1, :64]).logits[0, :, :256].float().cpu()
+    torch.testing.assert_close(logits, torch.from_numpy(g["logits"]), rtol=0, atol=0.05)

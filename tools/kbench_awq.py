@@ -1,0 +1,71 @@
+"""BASELINE.json configs[3] in miniature: INT4_AWQ_CFG (block-128, awq_lite) on ONE Llama-3-8B-shaped linear,
+mtq.quantize end to end on the GPU, ours vs the reference (oracle/_ref) on identical weights and batches.
+Prints wall time (synchronised), the chosen pre_quant_scale agreement and the number of kernels we launched."""
+
+from __future__ import annotations
+
+import copy
+import os
+import sys
+import time
+import warnings
+
+import torch
+from torch import nn
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tensorrt-model-optimizer_b200")]
+warnings.filterwarnings("ignore")
+
+
+def run(mtq, model, batches, cfg):
+    def loop(m):
+        for b in batches:
+            m(b)
+
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    with torch.no_grad():
+        mtq.quantize(model, cfg, loop)
+    torch.cuda.synchronize()
+    return time.perf_counter() - t0
+
+
+def main():
+    cout, cin = (int(v) for v in (sys.argv[1] if len(sys.argv) > 1 and "x" in sys.argv[1] else "4096x4096").split("x"))
+    torch.manual_seed(0)
+    base = nn.Sequential(nn.Linear(cin, cout, bias=False)).to("cuda", torch.bfloat16)
+    with torch.no_grad():
+        base[0].weight.mul_(0.5)
+        base[0].weight[:, ::97] *= 6.0        # a few salient input channels, what AWQ is for
+    batches = [torch.randn(8, 2048, cin, device="cuda", dtype=torch.bfloat16) * (1 + torch.rand(cin, device="cuda") * 3).to(torch.bfloat16)
+               for _ in range(2)]
+    import modelopt_b200 as ours
+    from modelopt_b200 import ops
+
+    res = {}
+    for rep in range(2):  # second repetition is the warm one
+        m = copy.deepcopy(base)
+        n0 = ops.LAUNCHES[0]
+        t = run(ours, m, batches, copy.deepcopy(ours.INT4_AWQ_CFG))
+        res["ours"] = (t, m[0].input_quantizer._pre_quant_scale.float().clone(), m[0].weight_quantizer._amax.float().clone(),
+                       ops.LAUNCHES[0] - n0)
+    print(f"ours      : {res['ours'][0] * 1e3:9.1f} ms   ({res['ours'][3]} kernel launches of this library)", flush=True)
+    ref_dir = os.path.join(ROOT, "oracle", "_ref")
+    if os.path.isdir(os.path.join(ref_dir, "modelopt")) and "--no-ref" not in sys.argv:
+        sys.path[:0] = [ref_dir, os.path.join(ROOT, "oracle", "ref_shims")]
+        import modelopt.torch.quantization as mtq
+
+        for rep in range(2):
+            m = copy.deepcopy(base)
+            t = run(mtq, m, batches, copy.deepcopy(mtq.INT4_AWQ_CFG))
+            res["ref"] = (t, m[0].input_quantizer._pre_quant_scale.float().clone(), m[0].weight_quantizer._amax.float().clone())
+        print(f"reference : {res['ref'][0] * 1e3:9.1f} ms   -> speed-up {res['ref'][0] / res['ours'][0]:.1f}x", flush=True)
+        a, b = res["ours"][1], res["ref"][1]
+        print(f"pre_quant_scale: max rel diff {((a - b).abs() / b.abs()).max().item():.3e}, identical {(a == b).float().mean().item() * 100:.1f}%")
+        a, b = res["ours"][2], res["ref"][2]
+        print(f"weight block amax: max rel diff {((a - b).abs() / b.abs().clamp_min(1e-30)).max().item():.3e}, identical {(a == b).float().mean().item() * 100:.1f}%")
+
+
+if __name__ == "__main__":
+    main()
