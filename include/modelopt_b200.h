@@ -231,6 +231,15 @@ int mo_sq_diff_mean(const void* a, const void* b, int64_t n, int dtype, double* 
 int mo_linear(const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K, int dtype,
               const void* ref, double* loss_acc, void* stream);
 
+/* mo_linear with the input quantizer fused into the GEMM's operand-A prologue: x is the RAW activation; four extra
+ * warps read each 128x64 tile from global memory, apply `prescale` (pre_quant_scale, fp32 [K], may be NULL) and the
+ * per-tensor fake-quant (fp8 = 1: E4M3 with `numerics`; else INT-`num_bits`, signed) in registers - the same arithmetic
+ * as mo_qdq_fp8_pqs / mo_qdq_int_pqs - and store the result straight into the swizzled shared-memory tile the MMA
+ * reads: `input_q(x)` never goes to HBM.  w is the (cached) fake-quantized weight.  x_amax: fp32 scalar on the device. */
+int mo_linear_qdq(const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K, int dtype,
+                  const float* x_amax, const float* prescale, int num_bits, int fp8, int narrow_range, int numerics,
+                  void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.

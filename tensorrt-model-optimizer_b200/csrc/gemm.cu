@@ -20,6 +20,7 @@
 #include <type_traits>
 
 #include "common.cuh"
+#include "qdq_ops.cuh"
 
 namespace mo {
 
@@ -27,6 +28,7 @@ constexpr int BM = 128, BN = 256, BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int kStages = 4;
 constexpr int kGemmThreads = 192;
+constexpr int kProThreads = 128;   // 4 extra warps that fake-quantize the A tile on its way into shared memory
 constexpr uint32_t kABytes = BM * BK * 2, kBBytes = BN * BK * 2, kStageBytes = kABytes + kBBytes;
 constexpr int kGroupM = 16;
 
@@ -110,6 +112,36 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t* r) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+// Operand-A prologue: the activation is read raw from global memory, multiplied by pre_quant_scale (optional) and
+// fake-quantized per tensor (FP8 E4M3 or INT-N) in registers, then written into the SWIZZLE_128B tile the MMA reads.
+struct ProArgs {
+  const void* x;       // raw activation [M, K]
+  const float* amax;   // fp32 scalar on the device
+  const float* pre;    // fp32 [K] pre_quant_scale (values of the operand dtype) or NULL
+  float maxb, minb;    // INT bounds
+  int eager;           // FP8: MO_NUMERICS_CPU scale arithmetic
+};
+
+template <typename T>
+__device__ __forceinline__ void unpack8(const uint4& v, float* f) {
+  V32 t;
+  t.w[0] = v.x; t.w[1] = v.y; t.w[2] = v.z; t.w[3] = v.w;
+  t.w[4] = t.w[5] = t.w[6] = t.w[7] = 0u;
+  float g[16];
+  Elem<T>::unpack(t, g);
+#pragma unroll
+  for (int i = 0; i < 8; ++i) f[i] = g[i];
+}
+template <typename T>
+__device__ __forceinline__ uint4 pack8(const float* f) {
+  float g[16];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { g[i] = f[i]; g[i + 8] = 0.f; }
+  V32 t;
+  Elem<T>::pack(g, t);
+  return make_uint4(t.w[0], t.w[1], t.w[2], t.w[3]);
+}
+
 struct TileCoord {
   int m_blk, n_blk;
 };
@@ -124,11 +156,12 @@ __device__ __forceinline__ TileCoord tile_coord(int tile, int tiles_m, int tiles
 }
 
 // kHalf: operands / output are f16 (else bf16).  kLoss: accumulate the squared error against `ref`, no store.
-template <bool kHalf, bool kLoss>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+// kPro: 0 = A arrives quantized through TMA; 1 = FP8 prologue; 2 = INT-N prologue (then 4 more warps run).
+template <bool kHalf, bool kLoss, int kPro>
+__global__ void __launch_bounds__(kGemmThreads + (kPro ? kProThreads : 0), 1)
 linear_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                       const void* __restrict__ bias_v, void* __restrict__ out_v, const void* __restrict__ ref_v,
-                      double* __restrict__ loss_acc, double loss_scale, int M, int N, int K) {
+                      double* __restrict__ loss_acc, double loss_scale, int M, int N, int K, ProArgs pro) {
   using T = typename std::conditional<kHalf, __half, __nv_bfloat16>::type;
   extern __shared__ uint8_t smem_raw[];
   GemmSmem& s = *reinterpret_cast<GemmSmem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -139,7 +172,8 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
-    for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
+    // full: the TMA thread's expect_tx arrive (+ one arrive per prologue warp)
+    for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], kPro ? 1 + kProThreads / 32 : 1); mbar_init(&s.empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&s.tmem_full[i], 1); mbar_init(&s.tmem_empty[i], 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -163,8 +197,8 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
         const TileCoord tc = tile_coord(tile, tiles_m, tiles_n);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&s.empty[stage], phase ^ 1);
-          mbar_expect_tx(&s.full[stage], kStageBytes);
-          tma_load_2d(s.a[stage], &map_a, &s.full[stage], kb * BK, tc.m_blk * BM);
+          mbar_expect_tx(&s.full[stage], kPro ? kBBytes : kStageBytes);
+          if constexpr (kPro == 0) tma_load_2d(s.a[stage], &map_a, &s.full[stage], kb * BK, tc.m_blk * BM);
           tma_load_2d(s.b[stage], &map_b, &s.full[stage], kb * BK, tc.n_blk * BN);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -196,6 +230,63 @@ linear_tcgen05_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_co
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (kPro != 0 && warp >= kGemmThreads / 32) {
+    // ===== operand-A prologue: 128 threads, 8 per 128-byte row segment, 16 rows per pass, 8 passes per stage =====
+    const int t = threadIdx.x - kGemmThreads;
+    const int chunk = t & 7, r0 = t >> 3;
+    const T* x = static_cast<const T*>(pro.x);
+    Fp8Op fop;
+    IntOp<false> iop;
+    if constexpr (kPro == 1) {
+      fop.ax.amax = pro.amax; fop.ax.mode = kPerTensor; fop.plain = false; fop.eager = pro.eager != 0;
+      fop.init();
+    } else {
+      iop.ax.amax = pro.amax; iop.ax.mode = kPerTensor; iop.maxb = pro.maxb; iop.minb = pro.minb; iop.status = nullptr;
+      iop.init();
+    }
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const TileCoord tc = tile_coord(tile, tiles_m, tiles_n);
+      const int m0 = tc.m_blk * BM;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int kcol = kb * BK + chunk * 8;
+        uint4 v[8];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {  // global loads first: they do not depend on the smem slot
+          const int row = m0 + r0 + 16 * p;
+          v[p] = (row < M && kcol < K) ? __ldg(reinterpret_cast<const uint4*>(x + (int64_t)row * K + kcol))
+                                       : make_uint4(0u, 0u, 0u, 0u);
+        }
+        float ps[8];
+        if (pro.pre != nullptr && kcol < K) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(pro.pre + kcol));
+          const float4 b = __ldg(reinterpret_cast<const float4*>(pro.pre + kcol + 4));
+          ps[0] = a.x; ps[1] = a.y; ps[2] = a.z; ps[3] = a.w; ps[4] = b.x; ps[5] = b.y; ps[6] = b.z; ps[7] = b.w;
+        }
+        mbar_wait(&s.empty[stage], phase ^ 1);
+        uint8_t* tile_a = s.a[stage];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+          float f[8];
+          unpack8<T>(v[p], f);
+          if (pro.pre != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) f[i] = __fmul_rn(f[i], ps[i]);
+            const uint4 tq = pack8<T>(f);   // the product is a tensor of the operand dtype in the reference
+            unpack8<T>(tq, f);
+          }
+          if constexpr (kPro == 1) fop.template vec<8>(f, 0); else iop.template vec<8>(f, 0);
+          const int r = r0 + 16 * p;
+          const uint32_t off = (uint32_t)((r >> 3) * 1024 + (r & 7) * 128 + ((chunk ^ (r & 7)) << 4));
+          *reinterpret_cast<uint4*>(tile_a + off) = pack8<T>(f);
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the MMA
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&s.full[stage]);
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
       }
     }
   } else {
@@ -310,10 +401,10 @@ static bool make_map(CUtensorMap* m, const void* base, int64_t rows, int64_t K, 
   return true;
 }
 
-template <bool kHalf, bool kLoss>
+template <bool kHalf, bool kLoss, int kPro = 0>
 static int linear_launch(const CUtensorMap& ma, const CUtensorMap& mb, const void* bias, void* out, const void* ref,
-                         double* loss_acc, int M, int N, int K, cudaStream_t s) {
-  auto kern = linear_tcgen05_kernel<kHalf, kLoss>;
+                         double* loss_acc, int M, int N, int K, cudaStream_t s, ProArgs pro = ProArgs{}) {
+  auto kern = linear_tcgen05_kernel<kHalf, kLoss, kPro>;
   const int smem = (int)sizeof(GemmSmem) + 1024;
   static bool configured = false;
   if (!configured) {
@@ -323,7 +414,8 @@ static int linear_launch(const CUtensorMap& ma, const CUtensorMap& mb, const voi
   }
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < kNumSMs ? tiles : kNumSMs;
-  kern<<<grid, kGemmThreads, smem, s>>>(ma, mb, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), M, N, K);
+  kern<<<grid, kGemmThreads + (kPro ? kProThreads : 0), smem, s>>>(ma, mb, bias, out, ref, loss_acc,
+                                                                    1.0 / ((double)M * (double)N), M, N, K, pro);
   return check_launch("mo_linear");
 }
 
@@ -351,4 +443,31 @@ extern "C" int mo_linear(const void* x, const void* w, const void* bias, void* o
                         : linear_launch<true, false>(ma, mb, bias, out, ref, loss_acc, m, n, k, s);
   return loss ? linear_launch<false, true>(ma, mb, bias, out, ref, loss_acc, m, n, k, s)
               : linear_launch<false, false>(ma, mb, bias, out, ref, loss_acc, m, n, k, s);
+}
+
+extern "C" int mo_linear_qdq(const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K,
+                             int dtype, const float* x_amax, const float* prescale, int num_bits, int fp8,
+                             int narrow_range, int numerics, void* stream) {
+  if (M < 0 || N < 0 || K < 0) { set_error("mo_linear_qdq: bad shape"); return MO_ERR_SHAPE; }
+  if (M == 0 || N == 0) return MO_OK;
+  if (dtype != MO_BF16 && dtype != MO_F16) { set_error("mo_linear_qdq: bf16 / f16 only (dtype %d)", dtype); return MO_ERR_DTYPE; }
+  if (!x || !w || !out || !x_amax) { set_error("mo_linear_qdq: NULL pointer"); return MO_ERR_NULL; }
+  if (K < 8 || K % 8 != 0 || N % 8 != 0) { set_error("mo_linear_qdq: K and N must be multiples of 8"); return MO_ERR_SHAPE; }
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) { set_error("mo_linear_qdq: dimension too large"); return MO_ERR_SHAPE; }
+  if (!fp8 && (num_bits < 2 || num_bits > 16)) { set_error("mo_linear_qdq: bad num_bits"); return MO_ERR_ARG; }
+  auto mis = [](const void* p) { return p && (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
+  if (mis(x) || mis(w) || mis(bias) || mis(out) || mis(prescale)) { set_error("mo_linear_qdq: pointers must be 16-byte aligned"); return MO_ERR_ARG; }
+  const bool half = dtype == MO_F16;
+  CUtensorMap ma, mb;
+  if (!make_map(&ma, x, M, K, BM, half) || !make_map(&mb, w, N, K, BN, half)) return MO_ERR_ARG;
+  ProArgs pro;
+  pro.x = x; pro.amax = x_amax; pro.pre = prescale; pro.eager = numerics == MO_NUMERICS_CPU;
+  pro.maxb = (float)((1 << (num_bits - 1)) - 1);
+  pro.minb = -(pro.maxb + (narrow_range ? 0.f : 1.f));
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int m = (int)M, n = (int)N, k = (int)K;
+  if (fp8) return half ? linear_launch<true, false, 1>(ma, mb, bias, out, nullptr, nullptr, m, n, k, s, pro)
+                       : linear_launch<false, false, 1>(ma, mb, bias, out, nullptr, nullptr, m, n, k, s, pro);
+  return half ? linear_launch<true, false, 2>(ma, mb, bias, out, nullptr, nullptr, m, n, k, s, pro)
+              : linear_launch<false, false, 2>(ma, mb, bias, out, nullptr, nullptr, m, n, k, s, pro);
 }

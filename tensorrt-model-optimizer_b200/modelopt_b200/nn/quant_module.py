@@ -190,6 +190,22 @@ class _QuantLinear(QuantLinearConvBase):
 
         return ops.linear_supported(input, w, self.bias)
 
+    @staticmethod
+    def _fused_input_format(q, input):
+        """num_bits of a per-tensor FP8 / signed INT input quantizer in plain quant mode, else None."""
+        from .. import ops
+
+        if (not isinstance(q, TensorQuantizer) or q._disabled or not q._if_quant or q._if_calib or not q._fake_quant
+                or q._dynamic or q.backend is not None or q.block_sizes is not None or q._use_constant_amax
+                or q._unsigned or getattr(q, "_bias", None) is not None or not hasattr(q, "_amax")
+                or q._amax.numel() != 1 or input.numel() // input.shape[-1] > ops.FUSED_PROLOGUE["max_rows"]):
+            return None
+        if q._num_bits == (4, 3):
+            return (4, 3) if ops.FUSED_PROLOGUE["fp8"] else None
+        if isinstance(q._num_bits, int) and 2 <= q._num_bits <= 16:
+            return q._num_bits if ops.FUSED_PROLOGUE["int"] else None
+        return None
+
     def quantized_weight(self):
         """weight_quantizer(weight), cached while neither the weight nor the quantizer state changes."""
         w = self._parameters["weight"]
@@ -212,7 +228,13 @@ class _QuantLinear(QuantLinearConvBase):
         if self._tcgen05_ok(input, args, kwargs):
             from .. import ops
 
-            out = ops.linear(self.input_quantizer(input), self.quantized_weight(), self.bias)
+            q = self.input_quantizer
+            fmt = self._fused_input_format(q, input)
+            if fmt is not None:  # input fake-quant inside the GEMM's operand prologue: ONE kernel for the linear
+                out = ops.linear_qdq(input, self.quantized_weight(), self.bias, q._amax, fmt, q._narrow_range,
+                                     prescale=q.pre_quant_scale)
+            else:
+                out = ops.linear(q(input), self.quantized_weight(), self.bias)
             return self.output_quantizer(out)
         return super().forward(input, *args, **kwargs)
 

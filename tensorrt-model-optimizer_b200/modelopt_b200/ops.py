@@ -690,3 +690,36 @@ def linear_loss_into(x, weight, bias, ref, acc):
         _launched(_lib.load().mo_linear(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None, None,
                                         M, N, K, _code(x2), r.data_ptr(), acc.data_ptr(), _stream(x)), "mo_linear")
     return acc
+
+
+# Which input formats take the fused-prologue GEMM, and up to how many rows of x.  Measured on B200
+# (profiles/r01_gemm_check.txt): at M = 16384 the prologue warps cannot keep up with the tensor pipe (1.13 ms vs 0.44 ms
+# for QDQ kernel + GEMM), so large batches use two kernels; the fused form is kept for small M where one launch and no
+# round trip of xq through HBM is what counts.
+FUSED_PROLOGUE = {"fp8": True, "int": True, "max_rows": 256}
+
+
+def linear_qdq(x, weight, bias, x_amax, num_bits=8, narrow_range=False, prescale=None, numerics=None, out=None):
+    """linear(fake_quant(x * prescale, x_amax), weight, bias) in ONE kernel: the per-tensor input fake-quant
+    (num_bits == (4, 3): FP8 E4M3, else signed INT-num_bits) runs in the GEMM's operand-A prologue."""
+    _cuda(x, "linear_qdq")
+    if not linear_supported(x, weight, bias):
+        raise ValueError("modelopt_b200.linear_qdq: unsupported operands")
+    x2 = x.contiguous().reshape(-1, x.shape[-1])
+    w = weight.contiguous()
+    b = bias.contiguous() if bias is not None else None
+    M, K = x2.shape
+    N = w.shape[0]
+    am = _f32_vec(x_amax, x2)
+    if am.numel() != 1:
+        raise ValueError("linear_qdq: per-tensor input amax only")
+    ps, _ = _prescale_vec(prescale, x2)
+    fp8 = num_bits == (4, 3)
+    y = torch.empty(*x.shape[:-1], N, dtype=x.dtype, device=x.device) if out is None else out
+    with _dev(x):
+        _launched(_lib.load().mo_linear_qdq(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None,
+                                            y.data_ptr(), M, N, K, _code(x2), am.data_ptr(),
+                                            ps.data_ptr() if ps is not None else None, 8 if fp8 else int(num_bits),
+                                            int(fp8), int(bool(narrow_range)), _mode(numerics), _stream(x)),
+                  "mo_linear_qdq")
+    return y

@@ -120,3 +120,41 @@ def test_quantized_weight_cache_invalidation():
         y3 = m(x)
         want = F.linear(lin.input_quantizer(x), lin.weight, lin.bias)
         torch.testing.assert_close(m[2](m[1](want)).float(), y3.float(), rtol=2.0 ** -6, atol=1e-2)
+
+
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (1000, 264, 72), (77, 520, 1024)])
+def test_linear_with_fused_input_quantizer_is_bit_identical_to_two_kernels(dt, M, N, K):
+    from modelopt_b200 import ops
+
+    torch.manual_seed(M + N + K + 1)
+    x = torch.randn(M, K, device="cuda", dtype=dt) * 2
+    w = torch.randn(N, K, device="cuda", dtype=dt) * 0.05
+    b = torch.randn(N, device="cuda", dtype=dt)
+    pqs = (torch.rand(K, device="cuda") + 0.5).to(dt)
+    am = x.float().abs().max() * 0.7
+    for fmt in ((4, 3), 8, 4):
+        for ps in (None, pqs):
+            xq = ops.qdq_fp8(x, am, prescale=ps) if fmt == (4, 3) else ops.qdq_int(x, am, fmt, False, False, prescale=ps)
+            assert torch.equal(ops.linear_qdq(x, w, b, am, fmt, False, prescale=ps), ops.linear(xq, w, b)), (fmt, ps is None)
+
+
+def test_quant_linear_small_batch_uses_one_kernel():
+    from modelopt_b200 import ops
+
+    m, data = _quant_linear("FP8_DEFAULT_CFG")
+    x = data[0][:1, :32]            # 32 rows <= FUSED_PROLOGUE["max_rows"]
+    with torch.no_grad():
+        m(x)                         # fills the weight caches
+        n0 = ops.LAUNCHES[0]
+        y = m(x)
+        assert ops.LAUNCHES[0] - n0 == 2          # one fused kernel per linear
+        old = dict(ops.FUSED_PROLOGUE)
+        ops.FUSED_PROLOGUE["max_rows"] = 0
+        try:
+            n0 = ops.LAUNCHES[0]
+            y2 = m(x)
+            assert ops.LAUNCHES[0] - n0 == 4      # input QDQ + GEMM per linear
+        finally:
+            ops.FUSED_PROLOGUE.update(old)
+    assert torch.equal(y, y2)
