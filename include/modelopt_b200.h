@@ -240,6 +240,20 @@ int mo_linear_qdq(const void* x, const void* w, const void* bias, void* out, int
                   const float* x_amax, const float* prescale, int num_bits, int fp8, int narrow_range, int numerics,
                   void* stream);
 
+/* NVFP4 W4A4 linear on the block-scaled tensor-core path (tcgen05.mma.kind::mxf4nvf4.block_scale), the role of the
+ * reference's real-quant NVFP4 GEMM backend (backends/nvfp4_gemm.py:28-125):
+ *   out[m,n] = T(a_gs*b_gs * sum_k (a[m,k]*a_sf[m,k/16]) * (b[n,k]*b_sf[n,k/16]) + bias[n])
+ * a_codes [M, K/2], b_codes [N, K/2]: packed E2M1 as mo_nvfp4_pack writes them; a_sf / b_sf: the E4M3 block scales
+ * re-ordered by mo_nvfp4_sf_swizzle (row_pad 128 for a, 256 for b); a_gs / b_gs: fp32 global scales on the device.
+ * K % 256 == 0, N % 8 == 0; out / bias dtype MO_BF16 or MO_F16. */
+int mo_linear_nvfp4(const void* a_codes, const void* a_sf, const float* a_gs, const void* b_codes, const void* b_sf,
+                    const float* b_gs, const void* bias, void* out, int64_t M, int64_t N, int64_t K, int out_dtype,
+                    void* stream);
+/* E4M3 block scales [rows, kblocks] row-major (mo_nvfp4_pack's sf_out) -> the 128-row x 4-block tile order of
+ * tcgen05 scale factors, rows zero-padded to a multiple of row_pad (128 or 256), kblocks to a multiple of 4. */
+int64_t mo_nvfp4_sf_swizzle_bytes(int64_t rows, int64_t kblocks, int row_pad);
+int mo_nvfp4_sf_swizzle(const void* sf, int64_t rows, int64_t kblocks, int row_pad, void* out, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.

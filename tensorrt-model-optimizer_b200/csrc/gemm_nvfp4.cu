@@ -1,0 +1,306 @@
+// NVFP4 W4A4 linear on the block-scaled tensor-core path:
+//   out[m,n] = T( alpha * sum_k (a[m,k] * sfa[m,k/16]) * (b[n,k] * sfb[n,k/16]) + bias[n] ),  alpha = gs_a * gs_b
+// a, b: packed E2M1 codes (two per byte, even element in the low nibble) as NVFP4QTensor.quantize / mo_nvfp4_pack
+// write them (reference qtensor/nvfp4_tensor.py:253-342); sfa, sfb: their E4M3 block scales re-ordered by
+// mo_nvfp4_sf_swizzle into the 128x4 tile order tcgen05 reads; gs_*: the fp32 global scales.  This is the role of the
+// reference's real-quant NVFP4 GEMM backend (backends/nvfp4_gemm.py:28-125, which needs TensorRT-LLM) and the
+// "kind::mxf4nvf4" path of SURVEY 7 step 9: the products of the DEQUANTIZED values are formed exactly by
+// tcgen05.mma.kind::mxf4nvf4.block_scale and accumulated in fp32 in TMEM.
+//
+// Kernel shape: as csrc/gemm.cu (TMA producer warp, single-thread MMA issuer, 4 epilogue warps, persistent grid), with
+//   * CTA tile 128 x 256, K step 256 elements (= 128 bytes of packed codes, one swizzle row), MMA K = 64;
+//   * per stage: A 16 KB + B 32 KB by cp.async.bulk.tensor, scale tiles 2 KB + 4 KB by cp.async.bulk;
+//   * scale factors go shared -> TMEM with tcgen05.cp.32x128b.warpx4 (4 columns per 128 rows x 64 K), double-buffered;
+//   * one 256-column accumulator (TMEM: 256 accumulator + 96 scale-factor columns).
+// Requirements: K % 256 == 0, N % 8 == 0; scale arrays padded as mo_nvfp4_sf_swizzle pads them.
+#include <type_traits>
+
+#include "tc_utils.cuh"
+
+namespace mo {
+
+namespace f4 {
+constexpr int BM = 128, BN = 256, BK = 256;          // BK in elements
+constexpr int kStages = 4;
+constexpr int kThreadsGemm = 192;
+constexpr uint32_t kABytes = BM * BK / 2, kBBytes = BN * BK / 2;      // 16 KB, 32 KB
+constexpr uint32_t kSfaBytes = (BM / 128) * (BK / 64) * 512;           // 2 KB
+constexpr uint32_t kSfbBytes = (BN / 128) * (BK / 64) * 512;           // 4 KB
+constexpr uint32_t kStageBytes = kABytes + kBBytes + kSfaBytes + kSfbBytes;
+constexpr int kGroupM = 16;
+constexpr uint32_t kAccCols = 256, kSfCols = 48;                        // per buffer: SFA 4x4 + SFB 4x8
+
+struct Smem {
+  uint8_t a[kStages][kABytes];
+  uint8_t b[kStages][kBBytes];
+  uint8_t sfa[kStages][kSfaBytes];
+  uint8_t sfb[kStages][kSfbBytes];
+  uint64_t full[kStages], empty[kStages], tmem_full, tmem_empty;
+  uint32_t tmem_base;
+};
+}  // namespace f4
+
+__device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// 32 rows x 16 bytes, rows contiguous (no swizzle): 8-row groups are 128 bytes apart.
+__device__ __forceinline__ uint64_t sf_desc(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)(128u >> 4) << 32;   // stride byte offset
+  d |= (uint64_t)1 << 46;             // descriptor version (sm_100)
+  return d;                           // layout type 0 = no swizzle, leading byte offset 0 (one 16-byte column)
+}
+__device__ __forceinline__ void utccp_32x128b(uint32_t tmem_dst, uint64_t desc) {
+  asm volatile("tcgen05.cp.cta_group::1.32x128b.warpx4 [%0], %1;" ::"r"(tmem_dst), "l"(desc) : "memory");
+}
+__device__ __forceinline__ void umma_nvfp4(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                           uint32_t sfa_tmem, uint32_t sfb_tmem, uint32_t accumulate) {
+  asm volatile(
+      "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n"
+      " tcgen05.mma.cta_group::1.kind::mxf4nvf4.block_scale.block16 [%0], %1, %2, %3, [%5], [%6], p;\n}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(sfa_tmem), "r"(sfb_tmem)
+      : "memory");
+}
+
+template <bool kHalf>
+__global__ void __launch_bounds__(f4::kThreadsGemm, 1)
+linear_nvfp4_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                    const uint8_t* __restrict__ sfa, const uint8_t* __restrict__ sfb,
+                    const float* __restrict__ gs_a, const float* __restrict__ gs_b, const void* __restrict__ bias_v,
+                    void* __restrict__ out_v, int M, int N, int K) {
+  using namespace f4;
+  using T = typename std::conditional<kHalf, __half, __nv_bfloat16>::type;
+  extern __shared__ uint8_t smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN, num_tiles = tiles_m * tiles_n;
+  const int num_kb = K / BK;
+  const int64_t sf_row_block_bytes = (int64_t)(K / 64) * 512;  // one 128-row block of scale factors
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
+    mbar_init(&s.tmem_full, 1);
+    mbar_init(&s.tmem_empty, 4);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = s.tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int per_group = kGroupM * tiles_n;
+        const int g = tile / per_group, r = tile - g * per_group;
+        const int gm = min(kGroupM, tiles_m - g * kGroupM);
+        const int n_blk = r / gm, m_blk = g * kGroupM + (r - n_blk * gm);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&s.empty[stage], phase ^ 1);
+          mbar_expect_tx(&s.full[stage], kStageBytes);
+          tma_load_2d(s.a[stage], &map_a, &s.full[stage], kb * (BK / 2), m_blk * BM);
+          tma_load_2d(s.b[stage], &map_b, &s.full[stage], kb * (BK / 2), n_blk * BN);
+          bulk_load(s.sfa[stage], sfa + (int64_t)m_blk * sf_row_block_bytes + (int64_t)kb * kSfaBytes, kSfaBytes,
+                    &s.full[stage]);
+#pragma unroll
+          for (int rb = 0; rb < BN / 128; ++rb)
+            bulk_load(s.sfb[stage] + rb * (kSfbBytes / (BN / 128)),
+                      sfb + (int64_t)(n_blk * (BN / 128) + rb) * sf_row_block_bytes + (int64_t)kb * (BK / 64) * 512,
+                      kSfbBytes / (BN / 128), &s.full[stage]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // block-scaled instruction descriptor: A/B = E2M1 (1), scale format UE4M3 (0), K-major, N>>3 @17, M>>4 @24
+      const uint32_t idesc = (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0, acc_phase = 0, it = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&s.tmem_empty, acc_phase ^ 1);
+        tc_fence_after();
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          mbar_wait(&s.full[stage], phase);
+          tc_fence_after();
+          const uint32_t sf_base = tmem + kAccCols + (it & 1u) * kSfCols;
+          const uint32_t sfa_s = smem_u32(s.sfa[stage]), sfb_s = smem_u32(s.sfb[stage]);
+#pragma unroll
+          for (int j = 0; j < BK / 64; ++j) {
+            utccp_32x128b(sf_base + 4 * j, sf_desc(sfa_s + j * 512));
+#pragma unroll
+            for (int rb = 0; rb < BN / 128; ++rb)
+              utccp_32x128b(sf_base + 16 + 8 * j + 4 * rb, sf_desc(sfb_s + rb * (BK / 64) * 512 + j * 512));
+          }
+          const uint64_t da = umma_desc(smem_u32(s.a[stage])), db = umma_desc(smem_u32(s.b[stage]));
+#pragma unroll
+          for (int j = 0; j < BK / 64; ++j)  // 64 elements = 32 bytes per MMA: +2 in the (>>4) address field
+            umma_nvfp4(tmem, da + (uint64_t)(2 * j), db + (uint64_t)(2 * j), idesc, sf_base + 4 * j,
+                       sf_base + 16 + 8 * j, (kb | j) != 0);
+          umma_commit(&s.empty[stage]);
+          if (kb == num_kb - 1) umma_commit(&s.tmem_full);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        acc_phase ^= 1;
+      }
+    }
+  } else {
+    const int quarter = warp & 3;
+    const T* bias = static_cast<const T*>(bias_v);
+    T* out = static_cast<T*>(out_v);
+    const float alpha = __fmul_rn(__ldg(gs_a), __ldg(gs_b));
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int per_group = kGroupM * tiles_n;
+      const int g = tile / per_group, r = tile - g * per_group;
+      const int gm = min(kGroupM, tiles_m - g * kGroupM);
+      const int n_blk = r / gm, m_blk = g * kGroupM + (r - n_blk * gm);
+      mbar_wait(&s.tmem_full, acc_phase);
+      tc_fence_after();
+      const int row = m_blk * BM + quarter * 32 + lane;
+      const int n0 = n_blk * BN;
+      const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t rr[32];
+        tmem_ld32(taddr + (uint32_t)c0, rr);
+        if (row < M) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const int col = n0 + c0 + j;
+            if (col < N) {
+              float f[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] = __fmul_rn(__uint_as_float(rr[j + i]), alpha);
+              if (bias != nullptr) {
+                const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
+                const T* bp = reinterpret_cast<const T*>(&bv);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = __fadd_rn(f[i], Elem<T>::load(bp + i));
+              }
+              uint4 o;
+              T* op = reinterpret_cast<T*>(&o);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) Elem<T>::store(op + i, f[i]);
+              *reinterpret_cast<uint4*>(out + (int64_t)row * N + col) = o;
+            }
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&s.tmem_empty);
+      acc_phase ^= 1;
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+  }
+}
+
+// E4M3 block scales [rows, kblocks] (row-major) -> 128 x 4 tiles: tile (rb, kq) at (rb * ceil(kblocks/4) + kq) * 512,
+// element (r, k) of the tile at (r % 32) * 16 + (r / 32) * 4 + k.  Rows are padded to `row_pad` (128 or 256) and
+// k-blocks to a multiple of 4 with zeros.
+__global__ void __launch_bounds__(kThreads) sf_swizzle_kernel(const uint8_t* __restrict__ sf, int64_t rows,
+                                                              int64_t kblocks, int64_t rows_padded,
+                                                              uint8_t* __restrict__ out) {
+  const int64_t kq_n = (kblocks + 3) / 4;
+  const int64_t total = rows_padded * kq_n;
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < total; i += (int64_t)gridDim.x * kThreads) {
+    const int64_t row = i / kq_n, kq = i - row * kq_n;
+    uint32_t v = 0;
+    if (row < rows) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int64_t kb = kq * 4 + k;
+        if (kb < kblocks) v |= (uint32_t)sf[row * kblocks + kb] << (8 * k);
+      }
+    }
+    const int64_t rb = row >> 7, r = row & 127;
+    *reinterpret_cast<uint32_t*>(out + (rb * kq_n + kq) * 512 + (r & 31) * 16 + (r >> 5) * 4) = v;
+  }
+}
+
+static bool make_map_u8(CUtensorMap* m, const void* base, int64_t rows, int64_t row_bytes, int box_rows) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return false; }
+  const cuuint64_t dims[2] = {(cuuint64_t)row_bytes, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)row_bytes};
+  const cuuint32_t box[2] = {128u, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return false; }
+  return true;
+}
+
+}  // namespace mo
+
+using namespace mo;
+
+extern "C" int64_t mo_nvfp4_sf_swizzle_bytes(int64_t rows, int64_t kblocks, int row_pad) {
+  if (rows < 0 || kblocks < 0 || (row_pad != 128 && row_pad != 256)) return -1;
+  const int64_t rp = (rows + row_pad - 1) / row_pad * row_pad;
+  return rp / 128 * ((kblocks + 3) / 4) * 512;
+}
+
+extern "C" int mo_nvfp4_sf_swizzle(const void* sf, int64_t rows, int64_t kblocks, int row_pad, void* out, void* stream) {
+  if (rows < 0 || kblocks < 0 || (row_pad != 128 && row_pad != 256)) { set_error("mo_nvfp4_sf_swizzle: bad arguments"); return MO_ERR_ARG; }
+  if (rows == 0 || kblocks == 0) return MO_OK;
+  if (!sf || !out) { set_error("mo_nvfp4_sf_swizzle: NULL pointer"); return MO_ERR_NULL; }
+  const int64_t rp = (rows + row_pad - 1) / row_pad * row_pad;
+  const int64_t total = rp * ((kblocks + 3) / 4);
+  sf_swizzle_kernel<<<persistent_grid((total + kThreads - 1) / kThreads, 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint8_t*>(sf), rows, kblocks, rp, static_cast<uint8_t*>(out));
+  return check_launch("mo_nvfp4_sf_swizzle");
+}
+
+extern "C" int mo_linear_nvfp4(const void* a_codes, const void* a_sf, const float* a_gs, const void* b_codes,
+                               const void* b_sf, const float* b_gs, const void* bias, void* out, int64_t M, int64_t N,
+                               int64_t K, int out_dtype, void* stream) {
+  if (M < 0 || N < 0 || K < 0) { set_error("mo_linear_nvfp4: bad shape"); return MO_ERR_SHAPE; }
+  if (M == 0 || N == 0) return MO_OK;
+  if (out_dtype != MO_BF16 && out_dtype != MO_F16) { set_error("mo_linear_nvfp4: bf16 / f16 output only"); return MO_ERR_DTYPE; }
+  if (!a_codes || !a_sf || !a_gs || !b_codes || !b_sf || !b_gs || !out) { set_error("mo_linear_nvfp4: NULL pointer"); return MO_ERR_NULL; }
+  if (K < f4::BK || K % f4::BK != 0 || N % 8 != 0) { set_error("mo_linear_nvfp4: K must be a multiple of %d and N of 8", f4::BK); return MO_ERR_SHAPE; }
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) { set_error("mo_linear_nvfp4: dimension too large"); return MO_ERR_SHAPE; }
+  auto mis = [](const void* p) { return p && (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
+  if (mis(a_codes) || mis(b_codes) || mis(a_sf) || mis(b_sf) || mis(bias) || mis(out)) { set_error("mo_linear_nvfp4: pointers must be 16-byte aligned"); return MO_ERR_ARG; }
+  CUtensorMap ma, mb;
+  if (!make_map_u8(&ma, a_codes, M, K / 2, f4::BM) || !make_map_u8(&mb, b_codes, N, K / 2, f4::BN)) return MO_ERR_ARG;
+  const int smem = (int)sizeof(f4::Smem) + 1024;
+  const bool half = out_dtype == MO_F16;
+  auto kern = half ? linear_nvfp4_kernel<true> : linear_nvfp4_kernel<false>;
+  static bool configured[2] = {false, false};
+  if (!configured[half]) {
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { set_error("mo_linear_nvfp4: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    configured[half] = true;
+  }
+  const int tiles = (int)(((M + f4::BM - 1) / f4::BM) * ((N + f4::BN - 1) / f4::BN));
+  const int grid = tiles < kNumSMs ? tiles : kNumSMs;
+  kern<<<grid, f4::kThreadsGemm, smem, static_cast<cudaStream_t>(stream)>>>(
+      ma, mb, static_cast<const uint8_t*>(a_sf), static_cast<const uint8_t*>(b_sf), a_gs, b_gs, bias, out, (int)M, (int)N,
+      (int)K);
+  return check_launch("mo_linear_nvfp4");
+}

@@ -723,3 +723,57 @@ def linear_qdq(x, weight, bias, x_amax, num_bits=8, narrow_range=False, prescale
                                             int(fp8), int(bool(narrow_range)), _mode(numerics), _stream(x)),
                   "mo_linear_qdq")
     return y
+
+
+# ------------------------------------------------------------------------------------------------
+# NVFP4 W4A4 linear on the block-scaled tensor-core path (csrc/gemm_nvfp4.cu)
+# ------------------------------------------------------------------------------------------------
+def nvfp4_sf_swizzle(sf, row_pad=128):
+    """E4M3 block scales [rows, kblocks] -> uint8 buffer in the 128 x 4 tile order tcgen05 reads (zero padded)."""
+    _cuda(sf, "nvfp4_sf_swizzle")
+    assert sf.element_size() == 1
+    sf2d = sf.contiguous().reshape(-1, sf.shape[-1])
+    rows, kblocks = sf2d.shape
+    lib = _lib.load()
+    nbytes = lib.mo_nvfp4_sf_swizzle_bytes(rows, kblocks, int(row_pad))
+    if nbytes < 0:
+        raise ValueError("nvfp4_sf_swizzle: row_pad must be 128 or 256")
+    out = torch.empty(nbytes, dtype=torch.uint8, device=sf.device)
+    with _dev(sf):
+        _launched(lib.mo_nvfp4_sf_swizzle(sf2d.data_ptr(), rows, kblocks, int(row_pad), out.data_ptr(), _stream(sf)),
+                  "mo_nvfp4_sf_swizzle")
+    return out
+
+
+def nvfp4_quantize_operand(x, global_amax, row_pad):
+    """x [rows, K] -> (codes [rows, K/2] uint8, swizzled scale buffer, fp32 global scale [1]) for linear_nvfp4;
+    the numbers are NVFP4QTensor.quantize's (global scale = amax / (6 * 448))."""
+    gs = div_scalar(_f32_vec(global_amax, x), 6.0 * 448.0)
+    codes, sf = nvfp4_pack(x, 16, gs)
+    return codes, nvfp4_sf_swizzle(sf, row_pad), gs
+
+
+def linear_nvfp4(a_codes, a_sf, a_gs, b_codes, b_sf, b_gs, bias=None, out_dtype=torch.bfloat16, out=None):
+    """out = (deq(a) @ deq(b)^T) + bias from packed NVFP4 operands (see nvfp4_quantize_operand), fp32 accumulation on
+    tcgen05.mma.kind::mxf4nvf4.block_scale."""
+    _cuda(a_codes, "linear_nvfp4")
+    a2 = a_codes.contiguous().reshape(-1, a_codes.shape[-1])
+    b2 = b_codes.contiguous()
+    M, K = a2.shape[0], a2.shape[1] * 2
+    N = b2.shape[0]
+    if b2.shape[1] * 2 != K or K % 256 or N % 8:
+        raise ValueError(f"linear_nvfp4: K={K} must be a multiple of 256 (both operands), N={N} of 8")
+    lib = _lib.load()
+    if a_sf.numel() != lib.mo_nvfp4_sf_swizzle_bytes(M, K // 16, 128) or \
+            b_sf.numel() != lib.mo_nvfp4_sf_swizzle_bytes(N, K // 16, 256):
+        raise ValueError("linear_nvfp4: scale buffers must come from nvfp4_sf_swizzle(row_pad=128 / 256)")
+    b = bias.contiguous() if bias is not None else None
+    if b is not None and (b.dtype != out_dtype or b.numel() != N):
+        raise ValueError("linear_nvfp4: bias must have the output dtype and N elements")
+    y = torch.empty(*a_codes.shape[:-1], N, dtype=out_dtype, device=a_codes.device) if out is None else out
+    code = _DT[out_dtype]
+    with _dev(a_codes):
+        _launched(lib.mo_linear_nvfp4(a2.data_ptr(), a_sf.data_ptr(), a_gs.data_ptr(), b2.data_ptr(), b_sf.data_ptr(),
+                                      b_gs.data_ptr(), b.data_ptr() if b is not None else None, y.data_ptr(), M, N, K,
+                                      code, _stream(a_codes)), "mo_linear_nvfp4")
+    return y
