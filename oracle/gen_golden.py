@@ -270,10 +270,10 @@ def gen_gpt2():
 
     import modelopt.torch.quantization as mtq
 
-    from oracle.models import gpt2_model_and_batches
+    from oracle.models import fingerprint, gpt2_model_and_batches
 
     model, batches = gpt2_model_and_batches()
-    g = {"w_fingerprint": to_np(torch.stack([p.double().abs().sum() for p in model.parameters()]))}
+    g = {"w_fingerprint": to_np(fingerprint(model))}
 
     def loop(m):
         with torch.no_grad():

@@ -31,6 +31,11 @@ def deterministic_fill_(model, seed: int = 0):
     return model
 
 
+def fingerprint(model) -> torch.Tensor:
+    """Order-independent exact checksum per parameter: the int64 sum of the fp32 bit patterns."""
+    return torch.stack([p.detach().float().contiguous().view(torch.int32).long().sum() for p in model.parameters()])
+
+
 def gpt2_model_and_batches():
     """BASELINE.json configs[0]: random-init GPT-2 small from its config (no checkpoint), fp32, 4 x [4, 512] tokens."""
     from transformers import GPT2Config, GPT2LMHeadModel

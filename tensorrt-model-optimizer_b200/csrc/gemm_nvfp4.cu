@@ -13,6 +13,8 @@
 //   * scale factors go shared -> TMEM with tcgen05.cp.32x128b.warpx4 (4 columns per 128 rows x 64 K), double-buffered;
 //   * one 256-column accumulator (TMEM: 256 accumulator + 96 scale-factor columns).
 // Requirements: K % 256 == 0, N % 8 == 0; scale arrays padded as mo_nvfp4_sf_swizzle pads them.
+#include <stdlib.h>
+
 #include <type_traits>
 
 #include "tc_utils.cuh"
@@ -28,14 +30,14 @@ constexpr uint32_t kSfaBytes = (BM / 128) * (BK / 64) * 512;           // 2 KB
 constexpr uint32_t kSfbBytes = (BN / 128) * (BK / 64) * 512;           // 4 KB
 constexpr uint32_t kStageBytes = kABytes + kBBytes + kSfaBytes + kSfbBytes;
 constexpr int kGroupM = 16;
-constexpr uint32_t kAccCols = 256, kSfCols = 48;                        // per buffer: SFA 4x4 + SFB 4x8
+constexpr uint32_t kAccCols = 256, kSfCols = 48;   // scale columns per stage: SFA 4 tiles x 4 + SFB 8 tiles x 4
 
 struct Smem {
   uint8_t a[kStages][kABytes];
   uint8_t b[kStages][kBBytes];
   uint8_t sfa[kStages][kSfaBytes];
   uint8_t sfb[kStages][kSfbBytes];
-  uint64_t full[kStages], empty[kStages], tmem_full, tmem_empty;
+  uint64_t full[kStages], empty[kStages], sf_ready[kStages], tmem_full, tmem_empty;
   uint32_t tmem_base;
 };
 }  // namespace f4
@@ -67,12 +69,31 @@ __device__ __forceinline__ void umma_nvfp4(uint32_t d_tmem, uint64_t a_desc, uin
       : "memory");
 }
 
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+      "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,"
+      "%30,%31,%32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+      "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+      "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+      "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
+
 template <bool kHalf>
 __global__ void __launch_bounds__(f4::kThreadsGemm, 1)
 linear_nvfp4_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                    const uint8_t* __restrict__ sfa, const uint8_t* __restrict__ sfb,
+                    const __grid_constant__ CUtensorMap map_sfa, const __grid_constant__ CUtensorMap map_sfb,
                     const float* __restrict__ gs_a, const float* __restrict__ gs_b, const void* __restrict__ bias_v,
-                    void* __restrict__ out_v, int M, int N, int K) {
+                    void* __restrict__ out_v, int M, int N, int K, int dbg) {
   using namespace f4;
   using T = typename std::conditional<kHalf, __half, __nv_bfloat16>::type;
   extern __shared__ uint8_t smem_raw[];
@@ -80,12 +101,14 @@ linear_nvfp4_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tiles_m = (M + BM - 1) / BM, tiles_n = (N + BN - 1) / BN, num_tiles = tiles_m * tiles_n;
   const int num_kb = K / BK;
-  const int64_t sf_row_block_bytes = (int64_t)(K / 64) * 512;  // one 128-row block of scale factors
+  const int sf_tiles_k = K / 64;  // 512-byte scale tiles per 128-row block
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
-    for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_sfa) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_sfb) : "memory");
+    for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); mbar_init(&s.sf_ready[i], 4); }
     mbar_init(&s.tmem_full, 1);
     mbar_init(&s.tmem_empty, 4);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -115,13 +138,12 @@ linear_nvfp4_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
           mbar_expect_tx(&s.full[stage], kStageBytes);
           tma_load_2d(s.a[stage], &map_a, &s.full[stage], kb * (BK / 2), m_blk * BM);
           tma_load_2d(s.b[stage], &map_b, &s.full[stage], kb * (BK / 2), n_blk * BN);
-          bulk_load(s.sfa[stage], sfa + (int64_t)m_blk * sf_row_block_bytes + (int64_t)kb * kSfaBytes, kSfaBytes,
-                    &s.full[stage]);
+          // scale tiles: rows of the [tiles, 128 x u32] view, BK/64 = 4 consecutive tiles per 128-row block
+          tma_load_2d(s.sfa[stage], &map_sfa, &s.full[stage], 0, m_blk * sf_tiles_k + kb * (BK / 64));
 #pragma unroll
           for (int rb = 0; rb < BN / 128; ++rb)
-            bulk_load(s.sfb[stage] + rb * (kSfbBytes / (BN / 128)),
-                      sfb + (int64_t)(n_blk * (BN / 128) + rb) * sf_row_block_bytes + (int64_t)kb * (BK / 64) * 512,
-                      kSfbBytes / (BN / 128), &s.full[stage]);
+            tma_load_2d(s.sfb[stage] + rb * (kSfbBytes / (BN / 128)), &map_sfb, &s.full[stage], 0,
+                        (n_blk * (BN / 128) + rb) * sf_tiles_k + kb * (BK / 64));
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -138,14 +160,19 @@ linear_nvfp4_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           mbar_wait(&s.full[stage], phase);
           tc_fence_after();
-          const uint32_t sf_base = tmem + kAccCols + (it & 1u) * kSfCols;
-          const uint32_t sfa_s = smem_u32(s.sfa[stage]), sfb_s = smem_u32(s.sfb[stage]);
+          const uint32_t sf_base = tmem + kAccCols + (uint32_t)stage * kSfCols;
+          if (dbg & 2) {  // debug: scale factors through tcgen05.cp from the MMA thread (12 copies per K step)
+            const uint32_t sfa_s = smem_u32(s.sfa[stage]), sfb_s = smem_u32(s.sfb[stage]);
 #pragma unroll
-          for (int j = 0; j < BK / 64; ++j) {
-            utccp_32x128b(sf_base + 4 * j, sf_desc(sfa_s + j * 512));
+            for (int j = 0; j < BK / 64; ++j) {
+              utccp_32x128b(sf_base + 4 * j, sf_desc(sfa_s + j * 512));
 #pragma unroll
-            for (int rb = 0; rb < BN / 128; ++rb)
-              utccp_32x128b(sf_base + 16 + 8 * j + 4 * rb, sf_desc(sfb_s + rb * (BK / 64) * 512 + j * 512));
+              for (int rb = 0; rb < BN / 128; ++rb)
+                utccp_32x128b(sf_base + 16 + 8 * j + 4 * rb, sf_desc(sfb_s + rb * (BK / 64) * 512 + j * 512));
+            }
+          } else {
+            mbar_wait(&s.sf_ready[stage], phase);  // the epilogue warps have written this stage's scale columns
+            tc_fence_after();
           }
           const uint64_t da = umma_desc(smem_u32(s.a[stage])), db = umma_desc(smem_u32(s.b[stage]));
 #pragma unroll
@@ -165,7 +192,40 @@ linear_nvfp4_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_cons
     T* out = static_cast<T*>(out_v);
     const float alpha = __fmul_rn(__ldg(gs_a), __ldg(gs_b));
     uint32_t acc_phase = 0;
+    int sf_stage = 0;
+    uint32_t sf_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      // Scale factors: shared memory -> registers -> TMEM (tcgen05.st), one stage ahead of the MMAs.  Every warp
+      // writes the same 48 columns into its own 32-lane quarter (the replication tcgen05.cp.warpx4 would do):
+      // lane l holds, per 128-row x 64-K tile, the 16 bytes [row l + 32c][k 0..3], c = 0..3 = four TMEM columns.
+      // A stage's TMEM columns are free again when its smem slot was refilled (full[stage] completes after the MMAs
+      // that read them have committed empty[stage]).
+      if (!(dbg & 2)) {
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&s.full[sf_stage], sf_phase);
+          const uint4* pa = reinterpret_cast<const uint4*>(s.sfa[sf_stage]) + lane;
+          const uint4* pb = reinterpret_cast<const uint4*>(s.sfb[sf_stage]) + lane;
+          uint32_t ra[16], rb_[32];
+#pragma unroll
+          for (int j = 0; j < BK / 64; ++j) {
+            const uint4 v = pa[j * 32];
+            ra[4 * j] = v.x; ra[4 * j + 1] = v.y; ra[4 * j + 2] = v.z; ra[4 * j + 3] = v.w;
+#pragma unroll
+            for (int rb = 0; rb < BN / 128; ++rb) {
+              const uint4 u = pb[(rb * (BK / 64) + j) * 32];
+              rb_[8 * j + 4 * rb] = u.x; rb_[8 * j + 4 * rb + 1] = u.y; rb_[8 * j + 4 * rb + 2] = u.z; rb_[8 * j + 4 * rb + 3] = u.w;
+            }
+          }
+          const uint32_t sf_t = tmem + ((uint32_t)(quarter * 32) << 16) + kAccCols + (uint32_t)sf_stage * kSfCols;
+          tmem_st16(sf_t, ra);
+          tmem_st32(sf_t + 16, rb_);
+          asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&s.sf_ready[sf_stage]);
+          if (++sf_stage == kStages) { sf_stage = 0; sf_phase ^= 1; }
+        }
+      }
       const int per_group = kGroupM * tiles_n;
       const int g = tile / per_group, r = tile - g * per_group;
       const int gm = min(kGroupM, tiles_m - g * kGroupM);
@@ -254,6 +314,21 @@ static bool make_map_u8(CUtensorMap* m, const void* base, int64_t rows, int64_t 
   return true;
 }
 
+// scale buffer as [n_tiles, 128] u32 (512-byte tiles), box = 4 tiles, no swizzle
+static bool make_map_sf(CUtensorMap* m, const void* base, int64_t n_tiles) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return false; }
+  const cuuint64_t dims[2] = {128u, (cuuint64_t)n_tiles};
+  const cuuint64_t strides[1] = {512u};
+  const cuuint32_t box[2] = {128u, (cuuint32_t)(f4::BK / 64)};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(m, CU_TENSOR_MAP_DATA_TYPE_UINT32, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (scales) failed (CUresult %d)", (int)r); return false; }
+  return true;
+}
+
 }  // namespace mo
 
 using namespace mo;
@@ -288,6 +363,9 @@ extern "C" int mo_linear_nvfp4(const void* a_codes, const void* a_sf, const floa
   if (mis(a_codes) || mis(b_codes) || mis(a_sf) || mis(b_sf) || mis(bias) || mis(out)) { set_error("mo_linear_nvfp4: pointers must be 16-byte aligned"); return MO_ERR_ARG; }
   CUtensorMap ma, mb;
   if (!make_map_u8(&ma, a_codes, M, K / 2, f4::BM) || !make_map_u8(&mb, b_codes, N, K / 2, f4::BN)) return MO_ERR_ARG;
+  CUtensorMap msa, msb;
+  if (!make_map_sf(&msa, a_sf, (M + 127) / 128 * (K / 64)) || !make_map_sf(&msb, b_sf, (N + 255) / 256 * 2 * (K / 64)))
+    return MO_ERR_ARG;
   const int smem = (int)sizeof(f4::Smem) + 1024;
   const bool half = out_dtype == MO_F16;
   auto kern = half ? linear_nvfp4_kernel<true> : linear_nvfp4_kernel<false>;
@@ -300,7 +378,6 @@ extern "C" int mo_linear_nvfp4(const void* a_codes, const void* a_sf, const floa
   const int tiles = (int)(((M + f4::BM - 1) / f4::BM) * ((N + f4::BN - 1) / f4::BN));
   const int grid = tiles < kNumSMs ? tiles : kNumSMs;
   kern<<<grid, f4::kThreadsGemm, smem, static_cast<cudaStream_t>(stream)>>>(
-      ma, mb, static_cast<const uint8_t*>(a_sf), static_cast<const uint8_t*>(b_sf), a_gs, b_gs, bias, out, (int)M, (int)N,
-      (int)K);
+      ma, mb, msa, msb, a_gs, b_gs, bias, out, (int)M, (int)N, (int)K, getenv("MO_DBG_NVFP4") ? atoi(getenv("MO_DBG_NVFP4")) : 0);
   return check_launch("mo_linear_nvfp4");
 }

@@ -224,10 +224,45 @@ class _QuantLinear(QuantLinearConvBase):
         self.__dict__["_wq_cache"] = (key, wq)
         return wq
 
+    # ---- opt-in: NVFP4 W4A4 on the block-scaled tensor-core path (real codes, not the bf16 simulation) ----
+    real_quant_gemm = False
+
+    @staticmethod
+    def _is_nvfp4_dynamic_calibrated(q):
+        return (isinstance(q, TensorQuantizer) and not q._disabled and q._if_quant and not q._if_calib
+                and q.is_nvfp4_dynamic and q.backend is None and hasattr(q, "_amax") and q.pre_quant_scale is None
+                and (q.block_sizes.get(-1) == 16))
+
+    def _real_nvfp4_ok(self, input):
+        w = self._parameters["weight"]
+        return (self.real_quant_gemm and self._is_nvfp4_dynamic_calibrated(self.input_quantizer)
+                and self._is_nvfp4_dynamic_calibrated(self.weight_quantizer) and not self.output_quantizer.is_enabled
+                and w.shape[1] % 256 == 0 and w.shape[0] % 8 == 0)
+
+    def packed_nvfp4_weight(self):
+        """(codes, swizzled scales, global scale) of the weight, cached like ``quantized_weight``."""
+        from .. import ops
+
+        w = self._parameters["weight"]
+        q = self.weight_quantizer
+        key = (w.data_ptr(), w._version, tuple(w.shape), w.dtype, q.cache_key())
+        hit = self.__dict__.get("_w4_cache")
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        with torch.no_grad():
+            packed = ops.nvfp4_quantize_operand(w.detach(), q._amax.float().amax(), 256)
+        self.__dict__["_w4_cache"] = (key, packed)
+        return packed
+
     def forward(self, input, *args, **kwargs):
         if self._tcgen05_ok(input, args, kwargs):
             from .. import ops
 
+            if self._real_nvfp4_ok(input):
+                a = ops.nvfp4_quantize_operand(input.reshape(-1, input.shape[-1]),
+                                               self.input_quantizer._amax.float().amax(), 128)
+                out = ops.linear_nvfp4(*a, *self.packed_nvfp4_weight(), self.bias, out_dtype=input.dtype)
+                return out.reshape(*input.shape[:-1], out.shape[-1])
             q = self.input_quantizer
             fmt = self._fused_input_format(q, input)
             if fmt is not None:  # input fake-quant inside the GEMM's operand prologue: ONE kernel for the linear
