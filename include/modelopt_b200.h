@@ -252,6 +252,11 @@ int mo_linear_nvfp4(const void* a_codes, const void* a_sf, const float* a_gs, co
 /* E4M3 block scales [rows, kblocks] row-major (mo_nvfp4_pack's sf_out) -> the 128-row x 4-block tile order of
  * tcgen05 scale factors, rows zero-padded to a multiple of row_pad (128 or 256), kblocks to a multiple of 4. */
 int64_t mo_nvfp4_sf_swizzle_bytes(int64_t rows, int64_t kblocks, int row_pad);
+/* mo_nvfp4_pack (block 16) for a [rows, cols] GEMM operand, cols % 64 == 0, writing the block scales directly in the
+ * swizzled order (buffer of mo_nvfp4_sf_swizzle_bytes(rows, cols/16, pad) bytes; the caller zero-fills it when rows is
+ * not a multiple of the pad): activation quantization for mo_linear_nvfp4 in ONE kernel. */
+int mo_nvfp4_pack_gemm(const void* x, int64_t rows, int64_t cols, int dtype, const float* sf2, uint8_t* codes,
+                       uint8_t* sf_swizzled, void* stream);
 int mo_nvfp4_sf_swizzle(const void* sf, int64_t rows, int64_t kblocks, int row_pad, void* out, void* stream);
 
 /* ------------------------------------------------------------------------------------------------

@@ -748,9 +748,22 @@ def nvfp4_sf_swizzle(sf, row_pad=128):
 def nvfp4_quantize_operand(x, global_amax, row_pad):
     """x [rows, K] -> (codes [rows, K/2] uint8, swizzled scale buffer, fp32 global scale [1]) for linear_nvfp4;
     the numbers are NVFP4QTensor.quantize's (global scale = amax / (6 * 448))."""
+    _cuda(x, "nvfp4_quantize_operand")
     gs = div_scalar(_f32_vec(global_amax, x), 6.0 * 448.0)
-    codes, sf = nvfp4_pack(x, 16, gs)
-    return codes, nvfp4_sf_swizzle(sf, row_pad), gs
+    x2 = x.contiguous().reshape(-1, x.shape[-1])
+    rows, cols = x2.shape
+    if cols % 64:
+        codes, sf = nvfp4_pack(x2, 16, gs)
+        return codes, nvfp4_sf_swizzle(sf, row_pad), gs
+    lib = _lib.load()
+    nbytes = lib.mo_nvfp4_sf_swizzle_bytes(rows, cols // 16, int(row_pad))
+    alloc = torch.empty if rows % row_pad == 0 else torch.zeros
+    sfw = alloc(nbytes, dtype=torch.uint8, device=x.device)
+    codes = torch.empty(rows, cols // 2, dtype=torch.uint8, device=x.device)
+    with _dev(x):
+        _launched(lib.mo_nvfp4_pack_gemm(x2.data_ptr(), rows, cols, _code(x2), gs.data_ptr(), codes.data_ptr(),
+                                         sfw.data_ptr(), _stream(x)), "mo_nvfp4_pack_gemm")
+    return codes, sfw, gs
 
 
 def linear_nvfp4(a_codes, a_sf, a_gs, b_codes, b_sf, b_gs, bias=None, out_dtype=torch.bfloat16, out=None):
