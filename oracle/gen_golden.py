@@ -264,6 +264,56 @@ def gen_mse():
     print("mse_cpu.npz", len(g), "arrays")
 
 
+def gen_awq_clip():
+    """The reference's awq_clip / awq_full on CPU (model_calib.py:1724-1940) on the tiny two-linear model: per-ratio
+    block losses (debug=True keeps them), the selected clip amax and the model output."""
+    import copy
+
+    import modelopt.torch.quantization as mtq
+
+    g = {}
+    gen = torch.Generator().manual_seed(11)
+    batches = [torch.randn(8, 16, 256, generator=gen) * (1 + i) for i in range(2)]
+    test = torch.randn(4, 16, 256, generator=gen) * 2
+    base = _tiny_model()
+    with torch.no_grad():  # a few outlier weights so that clipping below 1.0 wins in some blocks
+        base[0].weight[::7, ::13] *= 6.0
+        base[2].weight[::5, ::11] *= 6.0
+    for k, v in base.state_dict().items():
+        g[f"w_{k}"] = to_np(v)
+    for i, b in enumerate(batches):
+        g[f"batch{i}"] = to_np(b)
+    g["test"] = to_np(test)
+    cases = {
+        "int4_clip_t64": ("INT4_AWQ_CFG", {"method": "awq_clip", "debug": True}),
+        "int4_clip_t100": ("INT4_AWQ_CFG", {"method": "awq_clip", "max_tokens_per_batch": 100, "debug": True}),
+        "int4_clip_step": ("INT4_AWQ_CFG", {"method": "awq_clip", "min_clip_ratio": 0.3, "shrink_step": 0.05,
+                                            "debug": True}),
+        "int4_full": ("INT4_AWQ_CFG", {"method": "awq_full", "alpha_step": 0.1, "debug": True}),
+        "w4a8_clip": ("W4A8_AWQ_BETA_CFG", {"method": "awq_clip", "debug": True}),
+    }
+    for case, (name, algo) in cases.items():
+        cfg = copy.deepcopy(getattr(mtq, name))
+        cfg["algorithm"] = algo
+        m = mtq.quantize(copy.deepcopy(base), cfg, lambda model: [model(b) for b in batches])
+        for n, mod in m.named_modules():
+            if isinstance(mod, mtq.nn.TensorQuantizer):
+                g[f"{case}|{n}|enabled"] = np.asarray(mod.is_enabled)
+                for buf in ("_amax", "_pre_quant_scale"):
+                    if hasattr(mod, buf):
+                        g[f"{case}|{n}|{buf}"] = to_np(getattr(mod, buf).float())
+            if hasattr(mod, "awq_clip"):
+                h = mod.awq_clip
+                g[f"{case}|{n}|ratios"] = np.asarray(list(h.loss.keys()), dtype=np.float64)
+                g[f"{case}|{n}|loss"] = to_np(torch.stack([v.float() for v in h.loss.values()]))
+                g[f"{case}|{n}|w_amax"] = to_np(h.w_amax.float())
+                g[f"{case}|{n}|num_tokens"] = np.asarray(h.num_tokens)
+        with torch.no_grad():
+            g[f"{case}|out"] = to_np(m(test))
+    np.savez_compressed(os.path.join(OUT, "awq_clip_cpu.npz"), **g)
+    print("awq_clip_cpu.npz", len(g), "arrays")
+
+
 def gen_gpt2():
     """The reference's mtq.quantize(INT8_DEFAULT_CFG) on GPT-2 small on CPU: every quantizer's amax + a logits slice."""
     import copy
@@ -331,6 +381,6 @@ def gen_hist():
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
-    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack", "hist", "quantize", "mse", "gpt2"]
+    which = sys.argv[1:] or ["qdq", "fp4_scales", "amax", "nvfp4_pack", "hist", "quantize", "mse", "gpt2", "awq_clip"]
     for w in which:
         globals()["gen_" + w]()

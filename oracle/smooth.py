@@ -4,8 +4,9 @@ Follows modelopt/torch/quantization/model_calib.py:
   * smoothquant.postprocess (1304-1330) and apply_pre_quant_scale_and_smooth (1226-1270)
   * awq_lite: get_weight_scale (1453-1469), get_act_scale (1471-1472), get_scale (1474-1483), the search forward
     (1537-1551: weight_quantizer(W * s) with per-call block amax, input * (1/s)), update_loss (1485-1491)
+  * awq_clip: clip ratios (1761-1763), the blocked `_clip_search` (1813-1858), update_best_params (1787-1798)
 Parity pinning: tests/test_oracle_smooth.py reproduces the pre_quant_scale / folded weight / amax the REAL reference
-produced with mtq.quantize on CPU (tests/golden/quantize_cpu.npz) from these functions.
+produced with mtq.quantize on CPU (tests/golden/quantize_cpu.npz, awq_clip_cpu.npz) from these functions.
 """
 
 from __future__ import annotations
@@ -81,3 +82,39 @@ def awq_lite_linear(weight, bias, batches, block: int, num_bits: int = 4, alpha_
     vals = [float(l) for l in losses]
     best = alphas[min(range(len(alphas)), key=vals.__getitem__)]
     return alphas, vals, best, awq_get_scale(act, w_scale, best)
+
+
+def awq_clip_ratios(min_clip_ratio: float = 0.5, shrink_step: float = 0.05) -> list[float]:
+    """model_calib.py:1761-1763."""
+    return [round(float(k), 2) for k in torch.arange(min_clip_ratio, 1.0, shrink_step)] + [1.0]
+
+
+def awq_clip_block_losses(weight, tokens, w_amax, ratios, block: int, num_bits: int = 4) -> torch.Tensor:
+    """Blocked `_clip_search` for ONE batch of already sampled tokens (model_calib.py:1813-1858), without the
+    out-channel batching (it only bounds memory).  Returns [len(ratios), co, n_blocks] in fp32."""
+    co, ci = weight.shape
+    pad = (-ci) % block
+    w = F.pad(weight, (0, pad)) if pad else weight
+    x = F.pad(tokens, (0, pad)) if pad else tokens
+    wb = w.reshape(co, 1, -1, block)
+    xb = x.reshape(1, x.shape[0], -1, block)
+    org = (xb * wb).sum(dim=-1)                                           # [co, T, nb]
+    out = []
+    for r in ratios:
+        amax = (w_amax * r).reshape(co, -1, 1)
+        wq = int_qdq(w.reshape(co, -1, block), amax, num_bits, False, False).reshape(co, 1, -1, block)
+        cur = (xb * wq).sum(dim=-1)
+        out.append((cur - org).float().pow(2).mean(dim=1))                # [co, nb]
+    return torch.stack(out)
+
+
+def awq_clip_select(losses: torch.Tensor, w_amax: torch.Tensor, ratios) -> torch.Tensor:
+    """update_best_params (model_calib.py:1787-1798): first strict minimum over the ratios, in order."""
+    best_loss = torch.full_like(w_amax, float("inf"))
+    best = torch.zeros_like(w_amax)
+    for k, r in enumerate(ratios):
+        l = losses[k].view_as(w_amax)
+        take = l < best_loss
+        best_loss = torch.where(take, l, best_loss)
+        best = torch.where(take, w_amax * r, best)
+    return best

@@ -16,7 +16,7 @@ from typing import Any
 
 __all__ = ["QuantizerAttributeConfig", "normalize_quant_cfg_list", "INT8_DEFAULT_CFG", "INT8_SMOOTHQUANT_CFG",
            "FP8_DEFAULT_CFG", "NVFP4_DEFAULT_CFG", "INT4_AWQ_CFG", "INT4_BLOCKWISE_WEIGHT_ONLY_CFG",
-           "NVFP4_AWQ_LITE_CFG", "W4A8_AWQ_BETA_CFG", "choices"]
+           "NVFP4_AWQ_LITE_CFG", "W4A8_AWQ_BETA_CFG", "NVFP4_AWQ_CLIP_CFG", "NVFP4_AWQ_FULL_CFG", "choices"]
 
 _DEFAULTS: dict[str, Any] = {
     "enable": True,
@@ -225,7 +225,10 @@ NVFP4_DEFAULT_CFG = _preset(copy.deepcopy(_NVFP4), copy.deepcopy(_NVFP4), "max")
 INT4_BLOCKWISE_WEIGHT_ONLY_CFG = _preset(copy.deepcopy(_INT4_BLK), None, "max")
 INT4_AWQ_CFG = _preset(copy.deepcopy(_INT4_BLK), None, {"method": "awq_lite", "alpha_step": 0.1})
 NVFP4_AWQ_LITE_CFG = _preset(copy.deepcopy(_NVFP4), copy.deepcopy(_NVFP4), "awq_lite")
-W4A8_AWQ_BETA_CFG = _preset(copy.deepcopy(_INT4_BLK), {"num_bits": (4, 3), "axis": None}, "awq_lite")
+W4A8_AWQ_BETA_CFG = _preset([copy.deepcopy(_INT4_BLK), {"num_bits": (4, 3)}], {"num_bits": (4, 3)}, "awq_lite")
+NVFP4_AWQ_CLIP_CFG = _preset(copy.deepcopy(_NVFP4), copy.deepcopy(_NVFP4), {"method": "awq_clip"})
+NVFP4_AWQ_FULL_CFG = _preset(copy.deepcopy(_NVFP4), copy.deepcopy(_NVFP4), {"method": "awq_full", "alpha_step": 0.1})
 
 choices = {"INT8_DEFAULT_CFG", "INT8_SMOOTHQUANT_CFG", "FP8_DEFAULT_CFG", "NVFP4_DEFAULT_CFG", "INT4_AWQ_CFG",
-           "INT4_BLOCKWISE_WEIGHT_ONLY_CFG", "NVFP4_AWQ_LITE_CFG", "W4A8_AWQ_BETA_CFG"}
+           "INT4_BLOCKWISE_WEIGHT_ONLY_CFG", "NVFP4_AWQ_LITE_CFG", "W4A8_AWQ_BETA_CFG", "NVFP4_AWQ_CLIP_CFG",
+           "NVFP4_AWQ_FULL_CFG"}

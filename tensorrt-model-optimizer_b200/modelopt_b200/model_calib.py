@@ -12,6 +12,7 @@ alter any result:
 
 from __future__ import annotations
 
+import math
 import warnings
 
 import torch
@@ -580,13 +581,180 @@ def awq_lite(model: nn.Module, forward_loop=None, alpha_step: float = 0.1, debug
             delattr(module, "awq_lite")
 
 
+class AWQClipHelper:
+    """Per-linear clip-search state (model_calib.py:1746-1785).  ``loss_acc[k]`` is the accumulated loss of clip ratio
+    ``clip_ratios[k]``: one [co, n_blocks] fp32 plane per ratio (block search) or a scalar (per-tensor search)."""
+
+    def __init__(self, module, min_clip_ratio, shrink_step):
+        wq = module.weight_quantizer
+        self.num_tokens = 0
+        self.block_size = _get_awq_quantizer_block_size(module.weight, wq)
+        wq.reset_amax()
+        max_calibrate(wq, lambda q: q(module.weight), distributed_sync=False)
+        self.w_amax = wq.amax.clone()
+        co, ci = module.weight.shape
+        self.clip_ratios = [round(float(k), 2) for k in torch.arange(min_clip_ratio, 1.0, shrink_step)] + [1.0]
+        self.per_tensor = self.is_per_tensor_clip(module)
+        dev = module.weight.device
+        if self.per_tensor:
+            self.loss_acc = torch.zeros(len(self.clip_ratios), dtype=torch.float64, device=dev)
+        else:
+            self.loss_acc = torch.zeros(len(self.clip_ratios), co, math.ceil(ci / self.block_size), device=dev)
+        self.best_clip_val = None
+        self.best_loss = None
+        self.is_input_quantized = module.input_quantizer.is_enabled
+        wq.disable()
+
+    @property
+    def loss(self):
+        """{ratio: loss} like the reference's dict (views of ``loss_acc``)."""
+        return {r: self.loss_acc[k] for k, r in enumerate(self.clip_ratios)}
+
+    @staticmethod
+    def is_per_tensor_clip(module):
+        q = module.weight_quantizer
+        dynamic = q.block_sizes is not None and q.block_sizes.get("type", None) == "dynamic" and q.axis is None
+        return dynamic or (q.axis is None and q.block_sizes is None)
+
+    def update_best_params(self):
+        """First strict minimum over the ascending ratios (model_calib.py:1787-1798)."""
+        loss = self.loss_acc.float() if self.per_tensor else self.loss_acc
+        best_loss, best_k = loss.min(dim=0)  # torch.min returns the first index of the minimum
+        ratios = torch.tensor(self.clip_ratios, dtype=torch.float32, device=loss.device)
+        self.best_loss = best_loss.view_as(self.w_amax)
+        self.best_clip_val = self.w_amax * ratios[best_k].view_as(self.w_amax).to(self.w_amax.dtype)
+
+
+def _awq_clip_block_losses(module, h, tokens):
+    """Blocked branch of `_clip_search` (model_calib.py:1813-1858)."""
+    from . import ops
+
+    weight, q = module.weight, module.weight_quantizer
+    bs = h.block_size
+    fused = (weight.is_cuda and weight.dtype in (torch.float32, torch.float16, torch.bfloat16)
+             and tokens.dtype == weight.dtype and isinstance(q.num_bits, int) and bs <= ops.AWQ_CLIP_MAX_BLOCK
+             and weight.is_contiguous())
+    if fused:
+        ops.awq_clip_loss_into(weight.detach(), tokens, h.w_amax.float().contiguous().view(-1), h.clip_ratios,
+                               h.loss_acc, bs, num_bits=q.num_bits, unsigned=q.unsigned,
+                               narrow_range=q.narrow_range)
+        return
+    # any other block format: one batched GEMM per ratio on (Wq - W), blocks as the batch dimension
+    co, ci = weight.shape
+    pad = (-ci) % bs
+    x = torch.nn.functional.pad(tokens, (0, pad)) if pad else tokens
+    xb = x.reshape(x.shape[0], -1, bs).permute(1, 2, 0).float()                     # [nb, bs, T]
+    for k, shrink in enumerate(h.clip_ratios):
+        q.amax = h.w_amax * shrink
+        d = (q(weight) - weight).float()
+        d = torch.nn.functional.pad(d, (0, pad)) if pad else d
+        out = torch.bmm(d.reshape(co, -1, bs).permute(1, 0, 2), xb)                 # [nb, co, T]
+        h.loss_acc[k] += out.pow(2).mean(dim=-1).t()
+
+
+def _awq_clip_tensor_losses(module, h, inputs):
+    """Per-tensor branch (model_calib.py:1803-1812): only the global amax is clipped (NVFP4)."""
+    from . import ops
+
+    weight, q = module.weight, module.weight_quantizer
+    x2 = inputs.reshape(-1, inputs.shape[-1])
+    h.num_tokens += x2.shape[0]
+    fused = ops.linear_supported(x2, weight)
+    out_actual = ops.linear(x2, weight) if fused else x2 @ weight.T
+    original = q.amax.clone()
+    for k, shrink in enumerate(h.clip_ratios):
+        q.amax = original * shrink
+        wq = q(weight)
+        if fused:
+            ops.linear_loss_into(x2, wq, None, out_actual, h.loss_acc[k:k + 1])
+        else:
+            h.loss_acc[k] += (x2 @ wq.T - out_actual).float().pow(2).mean().double()
+
+
+def _awq_clip_forward(self, input, *args, **kwargs):
+    """The patched forward (model_calib.py:1860-1885)."""
+    h = self.awq_clip
+    if h.is_input_quantized:
+        self.input_quantizer.enable()
+        max_calibrate(self.input_quantizer, lambda q: q(input), distributed_sync=False)
+        self.input_quantizer.disable()
+    x = self.input_quantizer(input)
+    self.weight_quantizer.enable()
+    if h.per_tensor:
+        _awq_clip_tensor_losses(self, h, x)
+    else:
+        x2 = x.reshape(-1, x.shape[-1])
+        tokens = x2[0::max(1, x2.shape[0] // h.max_tokens)]
+        h.num_tokens += tokens.shape[0]
+        world = dist.get_world_size() if dist.is_available() and dist.is_initialized() else 1
+        if world > 1:  # the reference averages every batch's loss over the data-parallel group (:1849-1852)
+            before = h.loss_acc.clone()
+            _awq_clip_block_losses(self, h, tokens)
+            delta = h.loss_acc - before
+            dist.all_reduce(delta, op=dist.ReduceOp.SUM)
+            h.loss_acc = before + delta / world
+        else:
+            _awq_clip_block_losses(self, h, tokens)
+    self.weight_quantizer.disable()
+    return self._forward_no_awq(input, *args, **kwargs)
+
+
+@torch.no_grad()
+def awq_clip(model: nn.Module, forward_loop=None, max_co_batch_size: int = 1024, max_tokens_per_batch: int = 64,
+             min_clip_ratio: float = 0.5, shrink_step: float = 0.05, debug: bool = False, **_):
+    """model_calib.py:1724-1940.  ``max_co_batch_size`` is accepted for interface parity; the fused search keeps no
+    [co_bsz, tokens, n_block, block] temporaries, so there is nothing to batch."""
+    from .conversion import set_quantizer_by_cfg_context
+    from .utils import is_quantized_linear
+
+    assert forward_loop is not None, "forward_loop must be provided for awq_clip"
+    helpers = []
+    for name, module in model.named_modules():
+        if is_quantized_linear(module) and module.weight_quantizer.is_enabled \
+                and module.weight_quantizer.block_sizes is not None:
+            module.__dict__["_forward_no_awq"] = module.forward
+            module.forward = _awq_clip_forward.__get__(module)
+            module.awq_clip = AWQClipHelper(module, min_clip_ratio, shrink_step)
+            module.awq_clip.max_tokens = max_tokens_per_batch
+            helpers.append((name, module))
+
+    enable_stats_collection(model)
+    forward_loop(model)
+    with set_quantizer_by_cfg_context(model, [{"quantizer_name": "*weight_quantizer", "enable": False}]):
+        max_calibrate(model, lambda m: None, distributed_sync=True)
+    finish_stats_collection(model)
+
+    for name, module in helpers:
+        h = module.awq_clip
+        if h.num_tokens > 0:
+            h.update_best_params()
+            module.weight_quantizer.amax = h.best_clip_val
+            module.weight_quantizer.enable()
+            if h.is_input_quantized:
+                module.input_quantizer.enable()
+        module.__dict__.pop("forward", None)
+        module.__dict__.pop("_forward_no_awq", None)
+        if not debug:
+            delattr(module, "awq_clip")
+
+
 @torch.no_grad()
 def awq(model: nn.Module, forward_loop=None, algorithm: str = "awq_lite", **kwargs):
-    """model_calib.py:1362-1391 (awq_clip is not on this path)."""
-    if algorithm not in ("awq_lite",):
-        raise NotImplementedError(f"modelopt_b200: AWQ algorithm {algorithm!r} is not implemented (awq_lite only)")
+    """model_calib.py:1362-1391: ``awq_lite``, ``awq_clip`` or ``awq_full`` (lite, then clip)."""
+    import inspect
+
+    if algorithm not in ("awq_lite", "awq_clip", "awq_full"):
+        raise ValueError(f"modelopt_b200: unknown AWQ algorithm {algorithm!r}")
+
+    def own(fn):
+        names = inspect.signature(fn).parameters
+        return {k: v for k, v in kwargs.items() if k in names}
+
     with SequentialQuantizer.convert_to_single_quantizer(model):
-        awq_lite(model, forward_loop, **kwargs)
+        if algorithm in ("awq_full", "awq_lite"):
+            awq_lite(model, forward_loop, **own(awq_lite))
+        if algorithm in ("awq_full", "awq_clip"):
+            awq_clip(model, forward_loop, **own(awq_clip))
     from .utils import is_quantized_linear
 
     for module in model.modules():
@@ -594,4 +762,8 @@ def awq(model: nn.Module, forward_loop=None, algorithm: str = "awq_lite", **kwar
             max_calibrate(module, lambda lin: lin.weight_quantizer(lin.weight), distributed_sync=False)
 
 
-__all__ += ["awq_lite", "awq", "AWQLiteHelper"]
+def awq_full(model: nn.Module, forward_loop=None, **kwargs):
+    return awq(model, forward_loop, algorithm="awq_full", **kwargs)
+
+
+__all__ += ["awq_lite", "awq_clip", "awq_full", "awq", "AWQLiteHelper", "AWQClipHelper"]

@@ -24,10 +24,11 @@ ForwardLoop = Callable[[nn.Module], None]
 
 def _algorithms() -> dict[str | None, Callable]:
     table: dict[str | None, Callable] = {"max": model_calib.max_calibrate}
-    for name in ("smoothquant", "awq_lite", "awq_clip", "awq_full", "mse"):
-        fn = getattr(model_calib, name if name != "mse" else "mse_calibrate", None)
-        if fn is not None:
-            table[name] = fn
+    table["smoothquant"] = model_calib.smoothquant
+    table["mse"] = model_calib.mse_calibrate
+    for name in ("awq_lite", "awq_clip", "awq_full"):  # mode.py:236-238: every awq method goes through awq()
+        table[name] = (lambda method: lambda model, forward_loop=None, **kw:
+                       model_calib.awq(model, forward_loop, algorithm=method, **kw))(name)
     return table
 
 

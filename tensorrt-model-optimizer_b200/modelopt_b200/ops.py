@@ -3,6 +3,7 @@ plumbing here (device memory, current stream); all arithmetic happens in libmode
 
 from __future__ import annotations
 
+import ctypes as C
 import math
 import os
 
@@ -639,6 +640,33 @@ def sq_diff_mean_into(a, b, acc):
         _launched(_lib.load().mo_sq_diff_mean(a.data_ptr(), b.data_ptr(), a.numel(), _code(a), acc.data_ptr(),
                                               _stream(a)), "mo_sq_diff_mean")
     return acc
+
+
+AWQ_CLIP_MAX_BLOCK = 256
+_AWQ_CLIP_RATIOS_PER_LAUNCH = 12
+
+
+def awq_clip_loss_into(weight, tokens, w_amax, ratios, loss, block, num_bits=4, unsigned=False, narrow_range=False):
+    """loss[k, r, nb] += mean_t (sum_{j in block nb} tokens[t, j] * (QDQ_k(weight)[r, j] - weight[r, j]))^2 for every
+    clip ratio k (amax = w_amax * ratios[k]): the blocked branch of `_clip_search` (model_calib.py:1800-1858), all
+    ratios in one pass over the weight.  ``tokens`` is a 2-D view whose rows may be strided (``inputs[0::s]``)."""
+    _cuda(weight, "awq_clip_loss_into")
+    co, ci = weight.shape
+    assert tokens.dim() == 2 and tokens.shape[1] == ci and tokens.stride(1) == 1 and tokens.dtype == weight.dtype
+    assert weight.is_contiguous() and 1 <= block <= AWQ_CLIP_MAX_BLOCK
+    nb = -(-ci // block)
+    assert w_amax.dtype == torch.float32 and w_amax.numel() == co * nb and w_amax.is_contiguous()
+    assert loss.dtype == torch.float32 and tuple(loss.shape) == (len(ratios), co, nb) and loss.is_contiguous()
+    lib = _lib.load()
+    with _dev(weight):
+        for k0 in range(0, len(ratios), _AWQ_CLIP_RATIOS_PER_LAUNCH):
+            part = [float(r) for r in ratios[k0:k0 + _AWQ_CLIP_RATIOS_PER_LAUNCH]]
+            arr = (C.c_float * len(part))(*part)
+            _launched(lib.mo_awq_clip_loss(weight.data_ptr(), tokens.data_ptr(), co, ci, block, tokens.shape[0],
+                                           tokens.stride(0), _code(weight), w_amax.data_ptr(), arr, len(part), num_bits,
+                                           int(unsigned), int(narrow_range), loss[k0:].data_ptr(), _stream(weight)),
+                      "mo_awq_clip_loss")
+    return loss
 
 
 # ------------------------------------------------------------------------------------------------

@@ -43,12 +43,24 @@ def main():
     import modelopt_b200 as ours
     from modelopt_b200 import ops
 
+    algo = next((a.split("=", 1)[1] for a in sys.argv if a.startswith("--algo=")), "awq_lite")  # awq_clip, awq_full
+
+    def cfg_of(mod):
+        c = copy.deepcopy(mod.INT4_AWQ_CFG)
+        c["algorithm"] = {"method": algo} if algo == "awq_clip" else {"method": algo, "alpha_step": 0.1}
+        return c
+
+    def pqs(mod):
+        q = mod[0].input_quantizer
+        return q._pre_quant_scale.float().clone() if hasattr(q, "_pre_quant_scale") else torch.ones(1, device="cuda")
+
+    print(f"algorithm {algo}, linear {cout}x{cin}, 2 batches of 16384 tokens", flush=True)
     res = {}
     for rep in range(2):  # second repetition is the warm one
         m = copy.deepcopy(base)
         n0 = ops.LAUNCHES[0]
-        t = run(ours, m, batches, copy.deepcopy(ours.INT4_AWQ_CFG))
-        res["ours"] = (t, m[0].input_quantizer._pre_quant_scale.float().clone(), m[0].weight_quantizer._amax.float().clone(),
+        t = run(ours, m, batches, cfg_of(ours))
+        res["ours"] = (t, pqs(m), m[0].weight_quantizer._amax.float().clone(),
                        ops.LAUNCHES[0] - n0)
     print(f"ours      : {res['ours'][0] * 1e3:9.1f} ms   ({res['ours'][3]} kernel launches of this library)", flush=True)
     ref_dir = os.path.join(ROOT, "oracle", "_ref")
@@ -58,8 +70,8 @@ def main():
 
         for rep in range(2):
             m = copy.deepcopy(base)
-            t = run(mtq, m, batches, copy.deepcopy(mtq.INT4_AWQ_CFG))
-            res["ref"] = (t, m[0].input_quantizer._pre_quant_scale.float().clone(), m[0].weight_quantizer._amax.float().clone())
+            t = run(mtq, m, batches, cfg_of(mtq))
+            res["ref"] = (t, pqs(m), m[0].weight_quantizer._amax.float().clone())
         print(f"reference : {res['ref'][0] * 1e3:9.1f} ms   -> speed-up {res['ref'][0] / res['ours'][0]:.1f}x", flush=True)
         a, b = res["ours"][1], res["ref"][1]
         print(f"pre_quant_scale: max rel diff {((a - b).abs() / b.abs()).max().item():.3e}, identical {(a == b).float().mean().item() * 100:.1f}%")
