@@ -222,11 +222,13 @@ int mo_sq_diff_mean(const void* a, const void* b, int64_t n, int dtype, double* 
  * (row r of `co`, block nb of ceil(ci/block)) and every clip ratio k < n_ratio (<= 12 per call),
  *   loss[(k*co + r)*n_blocks + nb] += mean over the n_tok sampled tokens of
  *       ( sum_j x[t, j] * (QDQ(w[r, j]; amax = w_amax[r, nb] * ratios[k]) - w[r, j]) )^2 ,  j in block nb,
- * QDQ being the INT fake-quant of mo_qdq_int rounded to `dtype`.  Token t is the row x + t*tok_stride (the
+ * QDQ being the INT fake-quant of mo_qdq_int rounded to `dtype`; the product w_amax * ratio is rounded to `amax_dtype`
+ * first (the reference multiplies the amax tensor in ITS dtype: bf16 for a bf16 model).  Token t is the row x + t*tok_stride (the
  * reference's `inputs[0::stride]` sampling is a stride, not a copy).  `ratios` is a HOST array; w, x, w_amax, loss are
  * device pointers; block <= 256; columns past ci count as zeros (the reference pads). */
 int mo_awq_clip_loss(const void* w, const void* x, int64_t co, int64_t ci, int block, int64_t n_tok,
-                     int64_t tok_stride, int dtype, const float* w_amax, const float* ratios, int n_ratio,
+                     int64_t tok_stride, int dtype, const float* w_amax, int amax_dtype, const float* ratios,
+                     int n_ratio,
                      int num_bits, int is_unsigned, int narrow_range, float* loss, void* stream);
 
 /* ------------------------------------------------------------------------------------------------

@@ -39,7 +39,7 @@ template <typename T>
 __global__ void __launch_bounds__(kClipWarps * 32)
 awq_clip_loss_kernel(const T* __restrict__ w, const T* __restrict__ x, int64_t co, int64_t ci, int block,
                      int64_t n_blocks, int64_t n_tok, int64_t tok_stride, const float* __restrict__ w_amax,
-                     ClipRatios ratios, float minb, float maxb, float* __restrict__ loss) {
+                     ClipRatios ratios, int amax_dtype, float minb, float maxb, float* __restrict__ loss) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float* xT = reinterpret_cast<float*>(smem_raw);                                   // [block][kClipPitch]
   const int xt_words = (block * kClipPitch + 3) & ~3;
@@ -72,7 +72,9 @@ awq_clip_loss_kernel(const T* __restrict__ w, const T* __restrict__ x, int64_t c
         for (int k = 0; k < kClipMaxRatios; ++k) {
           d[k] = 0.f;
           if (k < ratios.n) {
-            const float a = __fmul_rn(am, ratios.r[k]);          // `w_amax * shrink` (:1826)
+            float a = __fmul_rn(am, ratios.r[k]);                // `w_amax * shrink` (:1826), in the amax dtype
+            if (amax_dtype == MO_BF16) a = __bfloat162float(__float2bfloat16_rn(a));
+            else if (amax_dtype == MO_F16) a = __half2float(__float2half_rn(a));
             float o = 0.f;
             if (!(a < kEps)) {                                    // tensor_quant_gpu.cu:46
               const float s = __fdiv_rn(maxb, a);
@@ -120,8 +122,8 @@ awq_clip_loss_kernel(const T* __restrict__ w, const T* __restrict__ x, int64_t c
 
 template <typename T>
 static int clip_launch(const void* w, const void* x, int64_t co, int64_t ci, int block, int64_t n_tok,
-                       int64_t tok_stride, const float* w_amax, const ClipRatios& ratios, float minb, float maxb,
-                       float* loss, cudaStream_t s) {
+                       int64_t tok_stride, const float* w_amax, const ClipRatios& ratios, int amax_dtype, float minb,
+                       float maxb, float* loss, cudaStream_t s) {
   const int64_t n_blocks = (ci + block - 1) / block;
   const size_t smem = (size_t)((block * kClipPitch + 3) & ~3) * sizeof(float) + (size_t)kClipWarps * 3 * block * sizeof(float4);
   static size_t configured = 0;
@@ -134,8 +136,8 @@ static int clip_launch(const void* w, const void* x, int64_t co, int64_t ci, int
   if (row_groups > 65535) { set_error("mo_awq_clip_loss: too many output channels (%lld)", (long long)co); return MO_ERR_SHAPE; }
   dim3 grid((unsigned)n_blocks, (unsigned)row_groups);
   awq_clip_loss_kernel<T><<<grid, kClipWarps * 32, smem, s>>>(static_cast<const T*>(w), static_cast<const T*>(x), co, ci,
-                                                             block, n_blocks, n_tok, tok_stride, w_amax, ratios, minb,
-                                                             maxb, loss);
+                                                             block, n_blocks, n_tok, tok_stride, w_amax, ratios,
+                                                             amax_dtype, minb, maxb, loss);
   return check_launch("mo_awq_clip_loss");
 }
 
@@ -144,7 +146,8 @@ static int clip_launch(const void* w, const void* x, int64_t co, int64_t ci, int
 using namespace mo;
 
 extern "C" int mo_awq_clip_loss(const void* w, const void* x, int64_t co, int64_t ci, int block, int64_t n_tok,
-                                int64_t tok_stride, int dtype, const float* w_amax, const float* ratios_host,
+                                int64_t tok_stride, int dtype, const float* w_amax, int amax_dtype,
+                                const float* ratios_host,
                                 int n_ratio, int num_bits, int is_unsigned, int narrow_range, float* loss,
                                 void* stream) {
   if (co < 0 || ci < 0 || n_tok < 0 || block < 1 || block > kClipMaxBlock || tok_stride < ci) {
@@ -155,6 +158,10 @@ extern "C" int mo_awq_clip_loss(const void* w, const void* x, int64_t co, int64_
   if (n_ratio < 1 || n_ratio > kClipMaxRatios) {
     set_error("mo_awq_clip_loss: n_ratio must be in [1, %d], got %d", kClipMaxRatios, n_ratio);
     return MO_ERR_ARG;
+  }
+  if (amax_dtype != MO_F32 && amax_dtype != MO_F16 && amax_dtype != MO_BF16) {
+    set_error("mo_awq_clip_loss: unsupported amax_dtype %d", amax_dtype);
+    return MO_ERR_DTYPE;
   }
   if (num_bits < 2 || num_bits > 16) { set_error("mo_awq_clip_loss: num_bits %d out of range", num_bits); return MO_ERR_ARG; }
   if (co == 0 || ci == 0 || n_tok == 0) return MO_OK;
@@ -167,9 +174,9 @@ extern "C" int mo_awq_clip_loss(const void* w, const void* x, int64_t co, int64_
   const float minb = -(bound + (narrow_range ? 0.f : 1.f));  // tensor_quant_gpu.cu:69 (also for unsigned)
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   switch (dtype) {
-    case MO_F32: return clip_launch<float>(w, x, co, ci, block, n_tok, tok_stride, w_amax, ratios, minb, maxb, loss, s);
-    case MO_F16: return clip_launch<__half>(w, x, co, ci, block, n_tok, tok_stride, w_amax, ratios, minb, maxb, loss, s);
-    case MO_BF16: return clip_launch<__nv_bfloat16>(w, x, co, ci, block, n_tok, tok_stride, w_amax, ratios, minb, maxb, loss, s);
+    case MO_F32: return clip_launch<float>(w, x, co, ci, block, n_tok, tok_stride, w_amax, ratios, amax_dtype, minb, maxb, loss, s);
+    case MO_F16: return clip_launch<__half>(w, x, co, ci, block, n_tok, tok_stride, w_amax, ratios, amax_dtype, minb, maxb, loss, s);
+    case MO_BF16: return clip_launch<__nv_bfloat16>(w, x, co, ci, block, n_tok, tok_stride, w_amax, ratios, amax_dtype, minb, maxb, loss, s);
   }
   set_error("mo_awq_clip_loss: unsupported dtype %d", dtype);
   return MO_ERR_DTYPE;

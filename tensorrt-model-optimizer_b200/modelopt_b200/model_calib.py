@@ -619,10 +619,13 @@ class AWQClipHelper:
     def update_best_params(self):
         """First strict minimum over the ascending ratios (model_calib.py:1787-1798)."""
         loss = self.loss_acc.float() if self.per_tensor else self.loss_acc
-        best_loss, best_k = loss.min(dim=0)  # torch.min returns the first index of the minimum
-        ratios = torch.tensor(self.clip_ratios, dtype=torch.float32, device=loss.device)
-        self.best_loss = best_loss.view_as(self.w_amax)
-        self.best_clip_val = self.w_amax * ratios[best_k].view_as(self.w_amax).to(self.w_amax.dtype)
+        self.best_loss = torch.full_like(self.w_amax, float("inf"), dtype=torch.float32)
+        self.best_clip_val = torch.zeros_like(self.w_amax)
+        for k, shrink in enumerate(self.clip_ratios):
+            cur = loss[k].view_as(self.w_amax)
+            take = cur < self.best_loss
+            self.best_loss = torch.where(take, cur, self.best_loss)
+            self.best_clip_val = torch.where(take, self.w_amax * shrink, self.best_clip_val)  # product in amax's dtype
 
 
 def _awq_clip_block_losses(module, h, tokens):
@@ -637,7 +640,7 @@ def _awq_clip_block_losses(module, h, tokens):
     if fused:
         ops.awq_clip_loss_into(weight.detach(), tokens, h.w_amax.float().contiguous().view(-1), h.clip_ratios,
                                h.loss_acc, bs, num_bits=q.num_bits, unsigned=q.unsigned,
-                               narrow_range=q.narrow_range)
+                               narrow_range=q.narrow_range, amax_dtype=h.w_amax.dtype)
         return
     # any other block format: one batched GEMM per ratio on (Wq - W), blocks as the batch dimension
     co, ci = weight.shape

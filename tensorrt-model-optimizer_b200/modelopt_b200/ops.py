@@ -646,10 +646,13 @@ AWQ_CLIP_MAX_BLOCK = 256
 _AWQ_CLIP_RATIOS_PER_LAUNCH = 12
 
 
-def awq_clip_loss_into(weight, tokens, w_amax, ratios, loss, block, num_bits=4, unsigned=False, narrow_range=False):
+def awq_clip_loss_into(weight, tokens, w_amax, ratios, loss, block, num_bits=4, unsigned=False, narrow_range=False,
+                       amax_dtype=torch.float32):
     """loss[k, r, nb] += mean_t (sum_{j in block nb} tokens[t, j] * (QDQ_k(weight)[r, j] - weight[r, j]))^2 for every
     clip ratio k (amax = w_amax * ratios[k]): the blocked branch of `_clip_search` (model_calib.py:1800-1858), all
-    ratios in one pass over the weight.  ``tokens`` is a 2-D view whose rows may be strided (``inputs[0::s]``)."""
+    ratios in one pass over the weight.  ``tokens`` is a 2-D view whose rows may be strided (``inputs[0::s]``);
+    ``w_amax`` is passed in fp32 and ``amax_dtype`` names the dtype the amax buffer really has (the candidate
+    ``w_amax * ratio`` is rounded to it, as the reference's tensor product is)."""
     _cuda(weight, "awq_clip_loss_into")
     co, ci = weight.shape
     assert tokens.dim() == 2 and tokens.shape[1] == ci and tokens.stride(1) == 1 and tokens.dtype == weight.dtype
@@ -663,7 +666,8 @@ def awq_clip_loss_into(weight, tokens, w_amax, ratios, loss, block, num_bits=4, 
             part = [float(r) for r in ratios[k0:k0 + _AWQ_CLIP_RATIOS_PER_LAUNCH]]
             arr = (C.c_float * len(part))(*part)
             _launched(lib.mo_awq_clip_loss(weight.data_ptr(), tokens.data_ptr(), co, ci, block, tokens.shape[0],
-                                           tokens.stride(0), _code(weight), w_amax.data_ptr(), arr, len(part), num_bits,
+                                           tokens.stride(0), _code(weight), w_amax.data_ptr(),
+                                           _DT[amax_dtype], arr, len(part), num_bits,
                                            int(unsigned), int(narrow_range), loss[k0:].data_ptr(), _stream(weight)),
                       "mo_awq_clip_loss")
     return loss

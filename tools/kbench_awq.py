@@ -61,7 +61,7 @@ def main():
         n0 = ops.LAUNCHES[0]
         t = run(ours, m, batches, cfg_of(ours))
         res["ours"] = (t, pqs(m), m[0].weight_quantizer._amax.float().clone(),
-                       ops.LAUNCHES[0] - n0)
+                       ops.LAUNCHES[0] - n0, m[0].weight_quantizer._amax.dtype)
     print(f"ours      : {res['ours'][0] * 1e3:9.1f} ms   ({res['ours'][3]} kernel launches of this library)", flush=True)
     ref_dir = os.path.join(ROOT, "oracle", "_ref")
     if os.path.isdir(os.path.join(ref_dir, "modelopt")) and "--no-ref" not in sys.argv:
@@ -71,10 +71,41 @@ def main():
         for rep in range(2):
             m = copy.deepcopy(base)
             t = run(mtq, m, batches, cfg_of(mtq))
-            res["ref"] = (t, pqs(m), m[0].weight_quantizer._amax.float().clone())
+            res["ref"] = (t, pqs(m), m[0].weight_quantizer._amax.float().clone(), 0, m[0].weight_quantizer._amax.dtype)
         print(f"reference : {res['ref'][0] * 1e3:9.1f} ms   -> speed-up {res['ref'][0] / res['ours'][0]:.1f}x", flush=True)
         a, b = res["ours"][1], res["ref"][1]
         print(f"pre_quant_scale: max rel diff {((a - b).abs() / b.abs()).max().item():.3e}, identical {(a == b).float().mean().item() * 100:.1f}%")
+        if algo == "awq_clip":
+            # which choice is better?  exact (fp64) clip-search objective of both amax sets on the sampled tokens
+            w = base[0].weight
+            tok = torch.cat([b.reshape(-1, cin)[0::max(1, b.numel() // cin // 64)] for b in batches]).double()
+            xb = tok.reshape(tok.shape[0], -1, 128)
+            for who in ("ours", "ref"):
+                am = res[who][2].reshape(-1, 1).contiguous()
+                wq = ops.qdq_int(w.reshape(-1, 128).contiguous(), am, num_bits=4, narrow_range=False).reshape(cout, -1, 128)
+                d = (wq.double() - w.reshape(cout, -1, 128).double())
+                tot = 0.0
+                for c0 in range(0, cout, 512):
+                    tot += torch.einsum("tnb,cnb->ctn", xb, d[c0:c0 + 512]).pow(2).sum().item()
+                print(f"exact clip objective with {who:4s} amax: {tot / tok.shape[0]:.6e}")
+            # lower bound: the per-block optimum of the exact objective over the 11 ratios (amax products in fp32)
+            w_amax = w.reshape(-1, 128).float().abs().amax(1, keepdim=True)
+            ratios = [round(0.5 + 0.05 * i, 2) for i in range(10)] + [1.0]
+            per = []
+            for r in ratios:
+                am = (w_amax * r).contiguous()
+                wq = ops.qdq_int(w.reshape(-1, 128).contiguous(), am, num_bits=4, narrow_range=False).reshape(cout, -1, 128)
+                d = (wq.double() - w.reshape(cout, -1, 128).double())
+                per.append(torch.cat([torch.einsum("tnb,cnb->ctn", xb, d[c0:c0 + 512]).pow(2).sum(1)
+                                      for c0 in range(0, cout, 512)]))
+            per = torch.stack(per)                                   # [11, co, nb]
+            best, k_best = per.min(0)
+            print(f"exact clip objective, per-block optimum : {best.sum().item() / tok.shape[0]:.6e}")
+            for who in ("ours", "ref"):
+                am = res[who][2].reshape(cout, -1)
+                k = ((am / w_amax.reshape(cout, -1)).unsqueeze(0) - torch.tensor(ratios, device="cuda").view(-1, 1, 1)).abs().argmin(0)
+                print(f"  {who:4s}: amax dtype {res[who][4]}, ratio index == exact optimum in {(k == k_best).float().mean().item() * 100:.1f}% of blocks,"
+                      f" histogram {torch.bincount(k.reshape(-1), minlength=11).tolist()}")
         a, b = res["ours"][2], res["ref"][2]
         print(f"weight block amax: max rel diff {((a - b).abs() / b.abs().clamp_min(1e-30)).max().item():.3e}, identical {(a == b).float().mean().item() * 100:.1f}%")
 
