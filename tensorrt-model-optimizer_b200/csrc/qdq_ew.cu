@@ -95,11 +95,10 @@ static int launch_stream(const void* x, void* y, int64_t n, Op op, cudaStream_t 
                    (pre == nullptr || (cols % E == 0 && (reinterpret_cast<uintptr_t>(pre) & 15u) == 0));
   int64_t tiles = vec ? (n / E + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll)
                       : (n + kThreads - 1) / kThreads;
-  const int grid = persistent_grid(tiles, 8);
   if (pre != nullptr)
-    qdq_stream_kernel<T, Op, true><<<grid, kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, pre, cols);
+    qdq_stream_kernel<T, Op, true><<<resident_grid((const void*)qdq_stream_kernel<T, Op, true>, tiles), kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, pre, cols);
   else
-    qdq_stream_kernel<T, Op, false><<<grid, kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, nullptr, 1);
+    qdq_stream_kernel<T, Op, false><<<resident_grid((const void*)qdq_stream_kernel<T, Op, false>, tiles), kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, nullptr, 1);
   return check_launch(what);
 }
 
@@ -226,7 +225,7 @@ static int blockdyn_launch(const void* x, void* y, int64_t n_blocks, int block, 
   if (vec) {
     const int64_t n_vec = n_blocks * lanes;
     const int64_t tiles = (n_vec + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll);
-    qdq_int_blockdyn_kernel<T, U><<<persistent_grid(tiles, 8), kThreads, 0, s>>>(
+    qdq_int_blockdyn_kernel<T, U><<<resident_grid((const void*)qdq_int_blockdyn_kernel<T, U>, tiles), kThreads, 0, s>>>(
         static_cast<const T*>(x), static_cast<T*>(y), n_vec, lanes, pre, cols, op, amax_out);
   } else {
     qdq_int_blockdyn_generic_kernel<T, U><<<persistent_grid((n_blocks * 32 + kThreads - 1) / kThreads, 8), kThreads, 0, s>>>(

@@ -261,10 +261,11 @@ static int launch_dynamic(const void* x, void* y, int64_t rows, int64_t cols, co
   if (vec) {
     const int64_t nb = rows * (cols / block);
     const int64_t tiles = (nb + (int64_t)kThreads * kUnrollB - 1) / ((int64_t)kThreads * kUnrollB);
-    const int grid = persistent_grid(tiles, 8);
-    if (block == 16) nvfp4_dynamic_kernel<T, 16, kIeee><<<grid, kThreads, 0, s>>>(xp, yp, nb, ga);
-    else if (block == 32) nvfp4_dynamic_kernel<T, 32, kIeee><<<grid, kThreads, 0, s>>>(xp, yp, nb, ga);
-    else nvfp4_dynamic_kernel<T, 64, kIeee><<<grid, kThreads, 0, s>>>(xp, yp, nb, ga);
+#define MO_DYN(B) nvfp4_dynamic_kernel<T, B, kIeee><<<resident_grid((const void*)nvfp4_dynamic_kernel<T, B, kIeee>, tiles), kThreads, 0, s>>>(xp, yp, nb, ga)
+    if (block == 16) MO_DYN(16);
+    else if (block == 32) MO_DYN(32);
+    else MO_DYN(64);
+#undef MO_DYN
   } else {
     const int64_t total = rows * ((cols + block - 1) / block);
     const int grid = persistent_grid((total + kThreads - 1) / kThreads, 8);
@@ -281,10 +282,11 @@ static int launch_static(const void* x, void* y, int64_t nb, int block, const fl
     constexpr int E = Elem<Tin>::kPerVec;
     if (aligned32(x) && aligned32(y) && (block == 16 || block == 32 || block == 64) && block % E == 0) {
       const int64_t tiles = (nb + (int64_t)kThreads * kUnrollB - 1) / ((int64_t)kThreads * kUnrollB);
-      const int grid = persistent_grid(tiles, 8);
-      if (block == 16) nvfp4_static_kernel<Tin, 16, kIeee><<<grid, kThreads, 0, s>>>(xp, yp, nb, scale);
-      else if (block == 32) nvfp4_static_kernel<Tin, 32, kIeee><<<grid, kThreads, 0, s>>>(xp, yp, nb, scale);
-      else nvfp4_static_kernel<Tin, 64, kIeee><<<grid, kThreads, 0, s>>>(xp, yp, nb, scale);
+#define MO_STA(B) nvfp4_static_kernel<Tin, B, kIeee><<<resident_grid((const void*)nvfp4_static_kernel<Tin, B, kIeee>, tiles), kThreads, 0, s>>>(xp, yp, nb, scale)
+      if (block == 16) MO_STA(16);
+      else if (block == 32) MO_STA(32);
+      else MO_STA(64);
+#undef MO_STA
       return check_launch("mo_qdq_nvfp4_static");
     }
   }

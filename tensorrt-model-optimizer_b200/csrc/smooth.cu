@@ -211,11 +211,11 @@ static int scale_cols_launch(const void* x, void* y, int64_t rows, int64_t cols,
                              int amax_mode, cudaStream_t st) {
   constexpr int E = Elem<T>::kPerVec;
   const bool vec = aligned32(x) && aligned32(y) && cols % E == 0 && (reinterpret_cast<uintptr_t>(s) & 15u) == 0;
-  const int grid = persistent_grid((rows * 32 + kThreads - 1) / kThreads, 8);
+  const int64_t tiles = (rows * 32 + kThreads - 1) / kThreads;
   if (vec)
-    scale_cols_kernel<T, true><<<grid, kThreads, 0, st>>>(static_cast<const T*>(x), static_cast<T*>(y), rows, cols, s, amax_bits, amax_mode);
+    scale_cols_kernel<T, true><<<resident_grid((const void*)scale_cols_kernel<T, true>, tiles), kThreads, 0, st>>>(static_cast<const T*>(x), static_cast<T*>(y), rows, cols, s, amax_bits, amax_mode);
   else
-    scale_cols_kernel<T, false><<<grid, kThreads, 0, st>>>(static_cast<const T*>(x), static_cast<T*>(y), rows, cols, s, amax_bits, amax_mode);
+    scale_cols_kernel<T, false><<<resident_grid((const void*)scale_cols_kernel<T, false>, tiles), kThreads, 0, st>>>(static_cast<const T*>(x), static_cast<T*>(y), rows, cols, s, amax_bits, amax_mode);
   return check_launch("mo_scale_cols_amax");
 }
 
