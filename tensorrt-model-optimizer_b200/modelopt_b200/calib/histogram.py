@@ -4,9 +4,10 @@
 whole bin widths afterwards, old counts are added to the prefix of the new histogram — but does it in one or
 two reads of the bf16 tensor instead of the reference's abs / float-copy / max / histc chain:
 
-* steady state: ONE kernel (``mo_hist``) bins |x| with the current range and folds max|x| in the same pass;
-  only if that max exceeded the range (the reference's ``x_max > edges[-1]``, a host decision there too) is the
-  batch re-binned with the grown range;
+* steady state: ONE kernel (``mo_hist``) adds the bins of |x| under the current range to the running counts and
+  folds max|x| in the same pass (plus a 4-byte memset and one 4-byte read); only if that max exceeded the range (the
+  reference's ``x_max > edges[-1]``, a host decision there too) is the batch taken out again and re-binned with the
+  grown range;
 * first batch: an amax pass fixes the range, then one binning pass.
 
 Counts are exact int64 (the reference's fp32 ``torch.histc`` stops counting at 2^24 per bin); ``_calib_hist``
@@ -39,6 +40,7 @@ class HistogramCalibrator(_Calibrator):
         self._skip_zeros = skip_zeros
         self._calib_bin_edges = None
         self._counts = None  # int64 device tensor
+        self._range_cache = None  # (edges object, device range_max, its bit pattern, amax scratch word)
         self._torch_hist = torch_hist
         # "cpu": build grown bin edges with torch.arange on the CPU (what the reference computes for CPU tensors;
         # CPU arange evaluates start + i*step in fp64, CUDA arange in fp32, so edges can differ in the last bit)
@@ -59,8 +61,8 @@ class HistogramCalibrator(_Calibrator):
         if x.dtype == torch.float64:
             x = x.float()
         dev = x.device
-        amax_bits = torch.zeros(1, dtype=torch.int32, device=dev)
         if self._counts is None:
+            amax_bits = torch.zeros(1, dtype=torch.int32, device=dev)
             ops.amax_into(x, 1, 1, x.numel(), amax_bits)
             x_max = amax_bits.view(torch.float32)
             self._check_finite(x_max)
@@ -70,11 +72,23 @@ class HistogramCalibrator(_Calibrator):
             self._calib_bin_edges = torch.linspace(0, x_max[0], self._num_bins + 1)  # histogram.py:118 (CPU tensor)
             return
         edges = self._calib_bin_edges
-        range_max = edges[-1:].to(device=dev, dtype=torch.float32)
-        new = torch.zeros(self._num_bins, dtype=torch.int64, device=dev)
-        ops.hist_into(x, range_max, new, amax_bits, self._skip_zeros)  # speculative: current range
-        x_max = amax_bits.view(torch.float32)
-        if bool(x_max[0] > range_max[0]) or bool(torch.isnan(x_max[0])):  # the reference's host branch (:121)
+        cache = self._range_cache
+        if cache is None or cache[0] is not edges or cache[1].device != dev:
+            range_max = edges[-1:].to(device=dev, dtype=torch.float32)
+            cache = self._range_cache = (edges, range_max, int(range_max.view(torch.int32).item()),
+                                         torch.zeros(1, dtype=torch.int32, device=dev))
+        _, range_max, range_bits, amax_bits = cache
+        # Steady state: ONE kernel adds this batch straight into the running counts with the current range and folds
+        # max|x| in the same read; the host then looks at one word (the reference's `x_max > edges[-1]` branch, :121,
+        # is a host decision too).  fp32 bit patterns of non-negative values order like the values, NaN above +inf.
+        amax_bits.zero_()
+        ops.hist_into(x, range_max, self._counts, amax_bits, self._skip_zeros)
+        if int(amax_bits.item()) > range_bits:
+            x_max = amax_bits.view(torch.float32)
+            # the range grows (rare): take the speculative batch out again, then re-bin it with the new range
+            undo = torch.zeros_like(self._counts)
+            ops.hist_into(x, range_max, undo, None, self._skip_zeros)
+            self._counts -= undo
             self._check_finite(x_max)
             width = edges[1] - edges[0]
             xm = x_max[0].to(width.device)
@@ -86,8 +100,8 @@ class HistogramCalibrator(_Calibrator):
             range_max = self._calib_bin_edges[-1:].to(dev).contiguous()
             new = torch.zeros(self._num_bins, dtype=torch.int64, device=dev)
             ops.hist_into(x, range_max, new, None, self._skip_zeros)
-        new[: self._counts.numel()] += self._counts
-        self._counts = new
+            new[: self._counts.numel()] += self._counts
+            self._counts = new
 
     @staticmethod
     def _check_finite(x_max):
@@ -98,6 +112,7 @@ class HistogramCalibrator(_Calibrator):
     def reset(self):
         self._calib_bin_edges = None
         self._counts = None
+        self._range_cache = None
 
     def compute_amax(self, method: str, *, stride: int = 1, start_bin: int = 128, percentile: float = 99.99,
                      intended_mse: bool = False):
