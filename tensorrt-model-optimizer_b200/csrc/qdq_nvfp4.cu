@@ -39,9 +39,12 @@ __device__ __forceinline__ float block_scale(float bmax, float gs, float six_gs)
 // Quantize-dequantize N values that share `s`; f in/out (fp32).
 template <int N, bool kIeee>
 __device__ __forceinline__ void qdq_block_values(float* f, float s) {
+  const DivSeq2 dv(s);  // IEEE mode: the division's own instruction sequence, reciprocal hoisted, packed fp32
 #pragma unroll
   for (int i = 0; i < N; i += 2) {
-    float a = div_mode<kIeee>(fabsf(f[i]), s), b = div_mode<kIeee>(fabsf(f[i + 1]), s);
+    float a = fabsf(f[i]), b = fabsf(f[i + 1]);
+    if (kIeee && dv.ok) dv(a, b);
+    else { a = div_mode<kIeee>(a, s); b = div_mode<kIeee>(b, s); }
     e2m1_roundtrip2(a, b);
     const float oa = __fmul_rn(s, a), ob = __fmul_rn(s, b);
     // reference: where(x >= 0, o, fma(-s, q, 0)); fma(-s,q,+0) == 0 - o (gives +0 for o == 0)

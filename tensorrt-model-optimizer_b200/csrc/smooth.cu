@@ -133,8 +133,15 @@ __global__ void __launch_bounds__(kThreads) col_sum_kernel(const T* __restrict__
       for (int o = 1; o < lanes_per_block; o <<= 1) m = max(m, __shfl_xor_sync(0xffffffffu, m, o));
       if (live) {
         const float den = round_T<T>(__fadd_rn(__uint_as_float(m), Tiny<T>::v));
+        const DivSeq2 dv(den);  // the division's own instruction sequence, reciprocal hoisted (common.cuh)
 #pragma unroll
-        for (int i = 0; i < E; ++i) acc[i] = __fadd_rn(acc[i], round_T<T>(__fdiv_rn(f[i], den)));
+        for (int i = 0; i < E; i += 2) {
+          float q0 = f[i], q1 = f[i + 1];
+          if (dv.ok) dv(q0, q1);
+          else { q0 = __fdiv_rn(q0, den); q1 = __fdiv_rn(q1, den); }
+          acc[i] = __fadd_rn(acc[i], round_T<T>(q0));
+          acc[i + 1] = __fadd_rn(acc[i + 1], round_T<T>(q1));
+        }
       }
     } else if (live) {
 #pragma unroll
