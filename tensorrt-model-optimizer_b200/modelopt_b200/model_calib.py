@@ -108,6 +108,15 @@ def max_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, **
             if ok and isinstance(m, TensorQuantizer) and not m._disabled and getattr(m, "_amax", None) is not None \
                     and not isinstance(getattr(m, "_calibrator", None), MaxCalibrator):
                 m.sync_amax_across_distributed_group(group)
+    _finalize_with_shared_state(model)
+
+
+def _finalize_with_shared_state(model: nn.Module, weight_patterns=None):
+    """model_calib.py:143-157: once every ``_amax`` is final (after the data-parallel sync), static-block weight
+    quantizers are promoted and fusible siblings (q/k/v, gate/up, w1/w3) get one shared NVFP4 ``global_amax``."""
+    from .utils import SHARED_PATTERNS, promote_static_block_weight_quantizers
+
+    promote_static_block_weight_quantizers(model, SHARED_PATTERNS if weight_patterns is None else weight_patterns)
 
 
 def sync_histograms(model: nn.Module, group=None):

@@ -32,7 +32,7 @@ try:
 except ImportError:  # pragma: no cover
     DTensor = None
 
-__all__ = ["TensorQuantizer", "SequentialQuantizer", "StaticBlockScaleQuantizer", "NVFP4StaticQuantizer",
+__all__ = ["TensorQuantizer", "SequentialQuantizer", "GroupedQuantizer", "StaticBlockScaleQuantizer", "NVFP4StaticQuantizer",
            "HardDisabledTensorQuantizer", "register_quant_backend", "unregister_quant_backend",
            "is_registered_quant_backend"]
 
@@ -800,6 +800,47 @@ class SequentialQuantizer(nn.Sequential):
         finally:
             for module, name, seq in swapped:
                 setattr(module, name, seq)
+
+
+class GroupedQuantizer(nn.ModuleList):
+    """One quantizer per weight of a grouped linear (fused experts: ``grouped[i](weight_i)``), tensor_quantizer.py:
+    1865-1892.  Unlike SequentialQuantizer the members act on DIFFERENT tensors; ``forward`` applies the first (the
+    single-weight compatibility path), ``amax`` / ``is_enabled`` / ``fake_quant`` read the first member and writes go to
+    all, lifecycle methods run on every member."""
+
+    _props = ("fake_quant", "is_enabled", "amax")
+    _methods = ("reset_amax", "disable", "enable", "load_calib_amax", "disable_quant", "enable_quant", "disable_calib",
+                "enable_calib")
+
+    def __init__(self, *quantizers):
+        super().__init__(quantizers)
+        assert len(self) and all(isinstance(q, (TensorQuantizer, SequentialQuantizer)) for q in self), \
+            "All quantizers must be a TensorQuantizer or SequentialQuantizer."
+
+    def forward(self, inputs):
+        return self[0](inputs)
+
+    def __getattr__(self, name):
+        if name in GroupedQuantizer._props:
+            return getattr(self[0], name)
+        if name in GroupedQuantizer._methods:
+            def call(*a, **k):
+                return [getattr(q, name)(*a, **k) for q in self]
+            return call
+        return super().__getattr__(name)
+
+    def __setattr__(self, name, value):
+        if name in GroupedQuantizer._props:
+            for q in self:
+                setattr(q, name, value)
+        else:
+            super().__setattr__(name, value)
+
+    def set_from_attribute_config(self, attributes):
+        if not isinstance(attributes, (list, tuple)):
+            attributes = [attributes] * len(self)
+        for a, q in zip(attributes, self):
+            q.set_from_attribute_config(a)
 
 
 class StaticBlockScaleQuantizer(TensorQuantizer):

@@ -17,7 +17,7 @@ from . import ops
 __all__ = ["fake_tensor_quant", "scaled_e4m3", "dynamic_block_quant", "static_blockwise_fp4_fake_quant",
            "fp4_cast_ste", "FakeTensorQuantFunction", "ScaledE4M3Function", "DynamicBlockQuantizationFunction",
            "StaticBlockwiseFP4FakeQuantFunction", "FP4CastSTEFunction", "fp8_eager", "quantize_op",
-           "dynamic_block_quantize_op"]
+           "dynamic_block_quantize_op", "OP_NAMESPACE", "int_cast_ste", "IntCastSTEFunction"]
 
 E4M3_MAX = 448.0
 mx_format_map = {(1, 2): "E1M2", (2, 1): "E2M1", (4, 3): "E4M3", (3, 2): "E3M2", (2, 3): "E2M3", (5, 2): "E5M2",
@@ -41,8 +41,8 @@ def fake_quant_impl(inputs, amax, num_bits=8, unsigned=False, narrow_range=True)
     return ops.qdq_int(inputs, amax, num_bits, unsigned, narrow_range)
 
 
-def quantize_op(inputs, amax, num_bits=8, exponent_bits=0, unsigned=False, narrow_range=True):
-    """Schema of ``tensorrt::quantize_op`` (tensor_quant.py:115-136, :222-229)."""
+def _quantize_impl(inputs, amax, num_bits=8, exponent_bits=0, unsigned=False, narrow_range=True):
+    """``tensorrt::quantize_op`` (tensor_quant.py:115-136, :222-229)."""
     if num_bits == 8 and exponent_bits == 4:
         return scaled_e4m3_impl(inputs, amax)
     if isinstance(num_bits, int):
@@ -50,8 +50,9 @@ def quantize_op(inputs, amax, num_bits=8, exponent_bits=0, unsigned=False, narro
     raise ValueError(f"Invalid combination of (num_bits, exponent_bits): ({num_bits}, {exponent_bits}).")
 
 
-def dynamic_block_quantize_op(inputs, block_size, amax, num_bits, exponent_bits, scale_num_bits, scale_exponent_bits):
-    """Schema of ``tensorrt::dynamic_block_quantize_op`` (tensor_quant.py:157-195, :231-237)."""
+def _dynamic_block_quantize_impl(inputs, block_size, amax, num_bits, exponent_bits, scale_num_bits,
+                                 scale_exponent_bits):
+    """``tensorrt::dynamic_block_quantize_op`` (tensor_quant.py:157-195, :231-237)."""
     scale_bits = (scale_exponent_bits, scale_num_bits - scale_exponent_bits - 1)
     fmt = (exponent_bits, num_bits - exponent_bits - 1) if exponent_bits != 0 else num_bits
     if fmt == (2, 1) and scale_bits == (4, 3):
@@ -61,6 +62,64 @@ def dynamic_block_quantize_op(inputs, block_size, amax, num_bits, exponent_bits,
         f"Unsupported num_bits: {fmt}, scale_bits: {scale_bits} for dynamic block quantization "
         "(modelopt_b200 implements NVFP4: E2M1 values with E4M3 block scales)."
     )
+
+
+# ------------------------------------------------------------------------------------------------ op registration
+def _register_library_ops():
+    """tensor_quant.py:216-276: the two functionals as ``torch.library`` operators with fake (shape-only)
+    implementations, so that ``torch.export`` / ``torch.compile`` can trace a quantized model without running a kernel.
+    Same schemas and, when free, the same ``tensorrt::`` names as the reference (an exported graph then carries the
+    node names its TensorRT consumers look for); if the reference itself is imported in this process and already owns
+    them, the ops go to ``modelopt_b200::``.  CUDA implementations only - there is no CPU kernel to register."""
+    schemas = {
+        "quantize_op": "(Tensor input, Tensor amax, int num_bits, int exponent_bits, bool unsigned, "
+                       "bool narrow_range) -> Tensor",
+        "dynamic_block_quantize_op": "(Tensor input, int block_size, Tensor amax, int num_bits, int exponent_bits, "
+                                     "int scale_num_bits, int scale_exponent_bits) -> Tensor",
+        "dynamic_block_quantize_op.overload": "(Tensor input, int block_size, None amax, int num_bits, "
+                                              "int exponent_bits, int scale_num_bits, int scale_exponent_bits) "
+                                              "-> Tensor",
+    }
+
+    def fake(input, *args, **kwargs):
+        return torch.empty_like(input)
+
+    def none_amax(inputs, block_size, amax, num_bits, exponent_bits, scale_num_bits, scale_exponent_bits):
+        return torch.empty_like(inputs)  # what the reference registers for this overload (:244-254)
+
+    impls = {"quantize_op": _quantize_impl, "dynamic_block_quantize_op": _dynamic_block_quantize_impl,
+             "dynamic_block_quantize_op.overload": none_amax}
+    for ns in ("tensorrt", "modelopt_b200"):
+        try:
+            for name, schema in schemas.items():
+                torch.library.define(f"{ns}::{name}", schema)
+            for name, fn in impls.items():
+                torch.library.impl(f"{ns}::{name}", ["cuda"])(fn)
+                torch.library.register_fake(f"{ns}::{name}")(fake)
+            return ns
+        except (AttributeError, RuntimeError):
+            continue
+    return None
+
+
+OP_NAMESPACE = _register_library_ops()
+
+
+def quantize_op(inputs, amax, num_bits=8, exponent_bits=0, unsigned=False, narrow_range=True):
+    """Eager calls go straight to the kernel wrapper (no dispatcher round trip per quantizer call); under
+    ``torch.compile`` / ``torch.export`` tracing the registered operator is used so that the graph keeps one node."""
+    if OP_NAMESPACE is not None and torch.compiler.is_compiling() and isinstance(amax, torch.Tensor):
+        return getattr(torch.ops, OP_NAMESPACE).quantize_op(inputs, amax, num_bits, exponent_bits, unsigned,
+                                                            narrow_range)
+    return _quantize_impl(inputs, amax, num_bits, exponent_bits, unsigned, narrow_range)
+
+
+def dynamic_block_quantize_op(inputs, block_size, amax, num_bits, exponent_bits, scale_num_bits, scale_exponent_bits):
+    if OP_NAMESPACE is not None and torch.compiler.is_compiling() and isinstance(amax, torch.Tensor):
+        return getattr(torch.ops, OP_NAMESPACE).dynamic_block_quantize_op(
+            inputs, block_size, amax, num_bits, exponent_bits, scale_num_bits, scale_exponent_bits)
+    return _dynamic_block_quantize_impl(inputs, block_size, amax, num_bits, exponent_bits, scale_num_bits,
+                                        scale_exponent_bits)
 
 
 # ------------------------------------------------------------------------------------------------ backward
@@ -186,7 +245,28 @@ class FP4CastSTEFunction(Function):
         return grad_outputs
 
 
+class IntCastSTEFunction(Function):
+    """tensor_quant.py:672-699: clamp(round(x)) to the INT-N range of already scaled values (the learned-scale branch of
+    the static block quantizer, tensor_quantizer.py:1697); backward passes the gradient inside the range only.  A
+    [min, max] clamp of a rounded tensor: two elementwise torch ops, used on weights during QAT, not on the PTQ path."""
+
+    @staticmethod
+    def forward(ctx, x, num_bits, unsigned=False, narrow_range=True):
+        max_bound = (2.0 ** (num_bits - 1 + int(unsigned))) - 1.0
+        min_bound = 0 if unsigned else (-max_bound if narrow_range else -max_bound - 1)
+        ctx.save_for_backward(x)
+        ctx.min_bound, ctx.max_bound = min_bound, max_bound
+        return torch.clamp(x.round(), min_bound, max_bound)
+
+    @staticmethod
+    def backward(ctx, grad_outputs):
+        (x,) = ctx.saved_tensors
+        inside = (x >= ctx.min_bound) & (x <= ctx.max_bound)
+        return torch.where(inside, grad_outputs, torch.zeros_like(grad_outputs)), None, None, None
+
+
 fake_tensor_quant = FakeTensorQuantFunction.apply
+int_cast_ste = IntCastSTEFunction.apply
 scaled_e4m3 = ScaledE4M3Function.apply
 dynamic_block_quant = DynamicBlockQuantizationFunction.apply
 static_blockwise_fp4_fake_quant = StaticBlockwiseFP4FakeQuantFunction.apply

@@ -134,3 +134,67 @@ def test_custom_backend_hook(mtq):
     assert not mtq.is_registered_quant_backend("ones")
     with pytest.raises(KeyError):
         m(torch.randn(2, 16, device="cuda"))
+
+
+def test_static_nvfp4_weights_promoted_with_shared_global_amax():
+    """max_calibrate ends with promote_static_block_weight_quantizers (model_calib.py:143-157, core_utils.py:1077-1150):
+    static NVFP4 weight quantizers become StaticBlockScaleQuantizer, q/k/v and gate/up siblings share one global_amax,
+    and the weight fake-quant is the two-level static kernel."""
+    import copy
+
+    import modelopt_b200 as mtq
+    from modelopt_b200 import ops
+    from modelopt_b200.nn import StaticBlockScaleQuantizer
+    from oracle import fake_quant as ofq
+
+    class Attn(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.q_proj, self.k_proj, self.v_proj = nn.Linear(64, 64), nn.Linear(64, 32), nn.Linear(64, 32)
+            self.o_proj = nn.Linear(64, 64)
+
+        def forward(self, x):
+            return self.o_proj(self.q_proj(x) + torch.cat([self.k_proj(x), self.v_proj(x)], -1))
+
+    class Net(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.attn = Attn()
+            self.gate_proj, self.up_proj = nn.Linear(64, 128), nn.Linear(64, 128)
+
+        def forward(self, x):
+            return self.attn(x).sum() + (self.gate_proj(x) * self.up_proj(x)).sum()
+
+    torch.manual_seed(3)
+    net = Net()
+    with torch.no_grad():
+        net.attn.k_proj.weight.mul_(3.0)
+        net.up_proj.weight.mul_(0.5)
+    net = net.cuda()
+    w4 = {"num_bits": (2, 1), "block_sizes": {-1: 16, "type": "static", "scale_bits": (4, 3)}}
+    cfg = {"quant_cfg": [{"quantizer_name": "*", "enable": False}, {"quantizer_name": "*weight_quantizer", "cfg": w4}],
+           "algorithm": "max"}
+    x = torch.randn(8, 64, device="cuda")
+    with torch.no_grad():
+        mtq.quantize(net, copy.deepcopy(cfg), lambda m: m(x))
+    lin = {n: m for n, m in net.named_modules() if isinstance(m, nn.Linear)}
+    for n, m in lin.items():
+        q = m.weight_quantizer
+        assert isinstance(q, StaticBlockScaleQuantizer) and q.is_nvfp4_static, n
+        assert q._amax.dtype == torch.float32 and q._global_amax.dtype == torch.float32
+        assert torch.equal(q._amax.view(-1).cpu(), m.weight.detach().cpu().reshape(-1, 16).abs().amax(1)), n
+    qkv = [lin[f"attn.{n}_proj"].weight_quantizer.global_amax for n in "qkv"]
+    want = max(lin[f"attn.{n}_proj"].weight.abs().max() for n in "qkv")
+    assert all(torch.equal(g.reshape(()), want.float().reshape(())) for g in qkv)
+    assert torch.equal(lin["gate_proj"].weight_quantizer.global_amax.reshape(()),
+                       torch.maximum(lin["gate_proj"].weight.abs().max(), lin["up_proj"].weight.abs().max()))
+    assert torch.equal(lin["attn.o_proj"].weight_quantizer.global_amax.reshape(()), lin["attn.o_proj"].weight.abs().max())
+    for n in ("attn.q_proj", "up_proj"):
+        m = lin[n]
+        q = m.weight_quantizer
+        with ops.numerics("cpu"):  # the oracle divides in IEEE fp32; the default GPU numerics are the Triton kernel's
+            got = q(m.weight).detach().cpu()
+        wc = m.weight.detach().cpu()
+        want_w = ofq.nvfp4_static_qdq(wc.reshape(-1, 16), q._amax.cpu().view(-1, 1), q._global_amax.cpu(), True, 448.0,
+                                      None).reshape(wc.shape)
+        assert torch.equal(got, want_w), n

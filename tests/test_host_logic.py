@@ -125,3 +125,33 @@ def test_cpu_tensors_fail_loudly_through_the_api(mtq):
     mtq.set_quantizer_by_cfg(m, mtq.FP8_DEFAULT_CFG["quant_cfg"])
     with pytest.raises(RuntimeError, match="no CPU fallback"):
         m(torch.randn(2, 16))
+
+
+def test_library_ops_registered_with_fake_impls():
+    """tensor_quant.py:216-276: the functionals are torch.library operators that trace without running a kernel."""
+    from torch._subclasses import FakeTensorMode
+
+    from modelopt_b200 import tensor_quant as tq
+
+    assert tq.OP_NAMESPACE in ("tensorrt", "modelopt_b200")
+    ns = getattr(torch.ops, tq.OP_NAMESPACE)
+    with FakeTensorMode():
+        x = torch.empty(4, 32, dtype=torch.bfloat16, device="cuda")
+        amax = torch.empty((), device="cuda")
+        assert ns.quantize_op(x, amax, 8, 0, False, True).shape == x.shape
+        assert ns.quantize_op(x, amax, 8, 4, False, False).dtype == torch.bfloat16
+        assert ns.dynamic_block_quantize_op(x, 16, amax, 4, 2, 8, 4).shape == x.shape
+    schema = str(ns.quantize_op.default._schema)
+    assert "Tensor input, Tensor amax, int num_bits, int exponent_bits, bool unsigned, bool narrow_range" in schema
+
+
+def test_int_cast_ste():
+    from modelopt_b200.tensor_quant import int_cast_ste
+
+    x = torch.tensor([-9.6, -8.0, 0.4, 0.5, 1.5, 7.7, 100.0], requires_grad=True)
+    y = int_cast_ste(x, 4, False, False)
+    assert y.tolist() == [-8.0, -8.0, 0.0, 0.0, 2.0, 7.0, 7.0]
+    y.sum().backward()
+    assert x.grad.tolist() == [0.0, 1.0, 1.0, 1.0, 1.0, 0.0, 0.0]
+    assert int_cast_ste(torch.tensor([-3.0, 20.0]), 4, True, True).tolist() == [0.0, 15.0]
+    assert int_cast_ste(torch.tensor([-9.0]), 4, False, True).tolist() == [-7.0]
