@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define MO_ABI_VERSION 2
+#define MO_ABI_VERSION 3
 
 typedef enum { MO_F32 = 0, MO_F16 = 1, MO_BF16 = 2 } mo_dtype;
 
@@ -270,6 +270,72 @@ int64_t mo_nvfp4_sf_swizzle_bytes(int64_t rows, int64_t kblocks, int row_pad);
 int mo_nvfp4_pack_gemm(const void* x, int64_t rows, int64_t cols, int dtype, const float* sf2, uint8_t* codes,
                        uint8_t* sf_swizzled, void* stream);
 int mo_nvfp4_sf_swizzle(const void* sf, int64_t rows, int64_t kblocks, int row_pad, void* out, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * MX formats and the remaining real-quant packers (rank 1).
+ * ---------------------------------------------------------------------------------------------- */
+/* Element / scale format codes = the reference's `Types` enum (gemm/tensor_quant_mx.h:39). */
+enum {
+  MO_FMT_E4M3 = 0, MO_FMT_E5M2 = 1, MO_FMT_INT8 = 2, MO_FMT_E0M3 = 3, MO_FMT_E1M2 = 4, MO_FMT_E3M0 = 5,
+  MO_FMT_E2M1 = 6, MO_FMT_E3M2 = 7, MO_FMT_E2M3 = 8, MO_FMT_E8M0 = 9
+};
+
+/* Replaces cuda_ext_mx.fused_amax_convert(inputs, block_size, format, scale_format, global_amax)
+ * (gemm/tensor_quant_mx.cu:347-387; called from tensor_quant.py:184-191 for MXFP8 / MXFP6 / MXFP4 / MXINT8 and every
+ * other dynamic block format): per block of `block` in {8,16,32} elements of the last dim (a short last block is
+ * zero-padded) compute amax, derive (scale, unscale) - E8M0: unscale = 2^ceil(log2(amax / format_max)) (:104-132);
+ * other scale formats: (:135-181) with the optional fp32 device scalar global_amax - and write
+ * y = sign(x) * format(|x| * scale) * unscale.  x / y: [rows, cols] contiguous, y == x allowed.
+ * numerics: MO_NUMERICS_GPU = the fp32 quotients are div.approx.ftz.f32 as in the reference's --use_fast_math build
+ * (quantization/extensions.py:69); MO_NUMERICS_CPU = IEEE quotients. */
+int mo_qdq_mx(const void* x, void* y, int64_t rows, int64_t cols, int dtype, int block, int format,
+              int scale_format, const float* global_amax, int numerics, void* stream);
+
+/* Replaces MXFP8QTensor.quantize / quantize_with_scale / get_weights_scaling_factor (qtensor/mxfp8_tensor.py:41-229).
+ * x: [rows, cols]; q: uint8 E4M3 codes [rows, cols]; sf: uint8 E8M0 bytes [rows, ceil(cols / 32)], written unless
+ * scale_given != 0 (then read).  q may be NULL with scale_given == 0 to compute only the scales. */
+int mo_mxfp8_pack(const void* x, uint8_t* q, uint8_t* sf, int64_t rows, int64_t cols, int dtype, int scale_given,
+                  int numerics, void* stream);
+/* Replaces MXFP4QTensor.quantize (qtensor/mxfp4_tensor.py:36-83).  x: n_blocks * block elements; q: uint8[n / 2], even
+ * element in the LOW nibble, nibble = sign << 3 | #{e2m1 bounds < |x / 2^e|} (a zero element carries the sign bit, ties
+ * round down, as written there); sf: uint8[n_blocks] = ceil(log2(amax / 6)) + 127. */
+int mo_mxfp4_pack(const void* x, uint8_t* q, uint8_t* sf, int64_t n_blocks, int block, int dtype, int numerics,
+                  void* stream);
+/* Replaces MXFP8QTensor.dequantize (kind 0, q = E4M3 codes [rows, cols]) and MXFP4QTensor.dequantize (kind 1, q =
+ * packed nibbles [rows, cols / 2]) (mxfp8_tensor.py:231-262, mxfp4_tensor.py:85-144): value * 2^(sf - 127) cast to
+ * out_dtype; sf: [rows, ceil(cols / block)]. */
+int mo_mx_unpack(const uint8_t* q, const uint8_t* sf, void* y, int64_t rows, int64_t cols, int block, int kind,
+                 int out_dtype, void* stream);
+
+/* Replaces INT4QTensor.quantize (qtensor/int4_tensor.py:39-88) = reduce_amax + `7 / amax` + cuda_ext.INT4_quantize
+ * (gemm/tensor_quant_gpu.cu:313-366) in ONE pass.  x: n_blocks * block elements of `dtype` (already padded);
+ * scales (out): n_blocks elements of the SAME dtype = T(T(1 / amax) * 7); q: uint8[n / 2], EVEN element in the HIGH
+ * nibble, nibble = code + 8.  numerics: MO_NUMERICS_GPU = the CUDA kernel's roundf(T(clamp(T(x * s), -8, 7) + 8)) in
+ * the tensor's own arithmetic; MO_NUMERICS_CPU = the eager round(T(x * s)).clamp(-8, 7) + 8. */
+int mo_int4_pack(const void* x, int64_t n_blocks, int block, int dtype, void* scales, uint8_t* q, int numerics,
+                 void* stream);
+/* Replaces cuda_ext.INT4_dequantize / the eager branch (int4_tensor.py:90-130): y[2i], y[2i+1] = (nibble - 8) / scale
+ * in the scales' dtype. */
+int mo_int4_unpack(const uint8_t* q, const void* scales, int64_t n_blocks, int block, int dtype, void* y, void* stream);
+/* Replaces NF4QTensor.quantize's first stage (qtensor/nf4_tensor.py:75-124, cuda_ext.NF4_quantize
+ * tensor_quant_gpu.cu:192-247): scales (out) = per-block amax in `dtype`, q = first-argmin table index of x / amax, even
+ * element in the high nibble.  numerics as for mo_int4_pack (kernel: fp32 table literals; eager: bf16 table values). */
+int mo_nf4_pack(const void* x, int64_t n_blocks, int block, int dtype, void* scales, uint8_t* q, int numerics,
+                void* stream);
+/* Replaces cuda_ext.NF4_dequantize (bf16_form = 1: bf16 table * bf16 scale -> bf16, out_dtype must be MO_BF16) and
+ * the eager branch (bf16_form = 0: bf16 table value * fp32 scale). scales: fp32 [n_blocks], already double-dequantized. */
+int mo_nf4_unpack(const uint8_t* q, const float* scales, int64_t n_blocks, int block, int out_dtype, int bf16_form,
+                  void* y, void* stream);
+
+/* Replaces INT8QTensor.quantize (kind 0, qtensor/int8_tensor.py:35-93) and FP8QTensor.quantize (kind 1,
+ * qtensor/fp8_tensor.py:38-115) for per-tensor, per-axis and N-D block scales.  x is viewed [O, A, I]; element (o, a, i)
+ * uses scales[(o / bo) * so + (a / ba) * sa + (i / bi) * si]; dims = {O, A, I, bo, ba, bi, so, sa, si} (host array).
+ * scales have x's dtype.  q = int8(clamp(round(T(x / s)), -128, 127)) or e4m3(T(x / s)). */
+int mo_q8_pack(const void* x, uint8_t* q, const void* scales, const int64_t* dims, int dtype, int kind, void* stream);
+/* Replaces INT8QTensor.dequantize / FP8QTensor.dequantize (int8_tensor.py:95-124, fp8_tensor.py:117-151):
+ * y = O(O(q) * O(scale)). */
+int mo_q8_unpack(const uint8_t* q, const void* scales, void* y, const int64_t* dims, int scale_dtype, int out_dtype,
+                 int kind, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).

@@ -15,7 +15,9 @@ MO_F32, MO_F16, MO_BF16 = 0, 1, 2
 MO_NUMERICS_GPU, MO_NUMERICS_CPU = 0, 1
 MO_DIV_TRITON, MO_DIV_IEEE = MO_NUMERICS_GPU, MO_NUMERICS_CPU
 MO_FLAG_NEGATIVE_IN_UNSIGNED, MO_FLAG_NEGATIVE_AMAX = 1, 2
-ABI_VERSION = 2
+# element / scale formats (the reference's `Types` enum order, gemm/tensor_quant_mx.h:39)
+MO_FMT = {"E4M3": 0, "E5M2": 1, "INT8": 2, "E0M3": 3, "E1M2": 4, "E3M0": 5, "E2M1": 6, "E3M2": 7, "E2M3": 8, "E8M0": 9}
+ABI_VERSION = 3
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 
@@ -53,6 +55,16 @@ SIGNATURES = {
     "mo_nvfp4_pack_gemm": [_p, _i64, _i64, _i, _p, _p, _p, _p],
     "mo_nvfp4_sf_swizzle_bytes": [_i64, _i64, _i],
     "mo_nvfp4_sf_swizzle": [_p, _i64, _i64, _i, _p, _p],
+    "mo_qdq_mx": [_p, _p, _i64, _i64, _i, _i, _i, _i, _p, _i, _p],
+    "mo_mxfp8_pack": [_p, _p, _p, _i64, _i64, _i, _i, _i, _p],
+    "mo_mxfp4_pack": [_p, _p, _p, _i64, _i, _i, _i, _p],
+    "mo_mx_unpack": [_p, _p, _p, _i64, _i64, _i, _i, _i, _p],
+    "mo_int4_pack": [_p, _i64, _i, _i, _p, _p, _i, _p],
+    "mo_int4_unpack": [_p, _p, _i64, _i, _i, _p, _p],
+    "mo_nf4_pack": [_p, _i64, _i, _i, _p, _p, _i, _p],
+    "mo_nf4_unpack": [_p, _p, _i64, _i, _i, _i, _p, _p],
+    "mo_q8_pack": [_p, _p, _p, C.POINTER(_i64), _i, _i, _p],
+    "mo_q8_unpack": [_p, _p, _p, C.POINTER(_i64), _i, _i, _i, _p],
     "mo_selftest_e2m1": [C.POINTER(C.c_uint64)],
     "mo_selftest_exact_div": [_i, _i, C.c_uint64, C.POINTER(C.c_uint64)],
     "mo_qdq_fp8_host": [_p, _p, _i64, _i, _f, _i],

@@ -15,6 +15,7 @@ from collections.abc import Mapping, Sequence
 from typing import Any
 
 __all__ = ["QuantizerAttributeConfig", "normalize_quant_cfg_list", "INT8_DEFAULT_CFG", "INT8_SMOOTHQUANT_CFG",
+           "MXFP8_DEFAULT_CFG", "MXFP6_DEFAULT_CFG", "MXFP4_DEFAULT_CFG", "MXINT8_DEFAULT_CFG", "W4A8_MXFP4_FP8_CFG",
            "FP8_DEFAULT_CFG", "NVFP4_DEFAULT_CFG", "INT4_AWQ_CFG", "INT4_BLOCKWISE_WEIGHT_ONLY_CFG",
            "NVFP4_AWQ_LITE_CFG", "W4A8_AWQ_BETA_CFG", "NVFP4_AWQ_CLIP_CFG", "NVFP4_AWQ_FULL_CFG", "choices"]
 
@@ -229,6 +230,21 @@ W4A8_AWQ_BETA_CFG = _preset([copy.deepcopy(_INT4_BLK), {"num_bits": (4, 3)}], {"
 NVFP4_AWQ_CLIP_CFG = _preset(copy.deepcopy(_NVFP4), copy.deepcopy(_NVFP4), {"method": "awq_clip"})
 NVFP4_AWQ_FULL_CFG = _preset(copy.deepcopy(_NVFP4), copy.deepcopy(_NVFP4), {"method": "awq_full", "alpha_step": 0.1})
 
-choices = {"INT8_DEFAULT_CFG", "INT8_SMOOTHQUANT_CFG", "FP8_DEFAULT_CFG", "NVFP4_DEFAULT_CFG", "INT4_AWQ_CFG",
+
+
+def _mx(num_bits):
+    # modelopt_recipes/configs/numerics/mx{fp8,fp6,fp4,int8}.yaml
+    return {"num_bits": num_bits, "block_sizes": {-1: 32, "type": "dynamic", "scale_bits": (8, 0)}}
+
+
+# modelopt_recipes/configs/ptq/presets/model/mx*.yaml, w4a8_mxfp4_fp8.yaml (config.py:1708-1714): algorithm is None
+MXFP8_DEFAULT_CFG = _preset(_mx((4, 3)), _mx((4, 3)), None)
+MXFP6_DEFAULT_CFG = _preset(_mx((3, 2)), _mx((3, 2)), None)
+MXFP4_DEFAULT_CFG = _preset(_mx((2, 1)), _mx((2, 1)), None)
+MXINT8_DEFAULT_CFG = _preset(_mx(8), _mx(8), None)
+W4A8_MXFP4_FP8_CFG = _preset(_mx((2, 1)), {"num_bits": (4, 3), "axis": None}, None)
+
+choices = {"MXFP8_DEFAULT_CFG", "MXFP6_DEFAULT_CFG", "MXFP4_DEFAULT_CFG", "MXINT8_DEFAULT_CFG", "W4A8_MXFP4_FP8_CFG",
+           "INT8_DEFAULT_CFG", "INT8_SMOOTHQUANT_CFG", "FP8_DEFAULT_CFG", "NVFP4_DEFAULT_CFG", "INT4_AWQ_CFG",
            "INT4_BLOCKWISE_WEIGHT_ONLY_CFG", "NVFP4_AWQ_LITE_CFG", "W4A8_AWQ_BETA_CFG", "NVFP4_AWQ_CLIP_CFG",
            "NVFP4_AWQ_FULL_CFG"}

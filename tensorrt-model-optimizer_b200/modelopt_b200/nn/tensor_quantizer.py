@@ -25,6 +25,7 @@ from torch import nn
 from .. import calib
 from ..config import QuantizerAttributeConfig
 from ..tensor_quant import (dynamic_block_quant, fake_tensor_quant, scaled_e4m3, static_blockwise_fp4_fake_quant)
+from .. import ops
 from ..utils import convert_quantization_axis_to_reduce_axis, reduce_amax
 
 try:
@@ -150,7 +151,7 @@ class TensorQuantizer(nn.Module):
             name, setter = custom.get(attribute, (f"_{attribute}", lambda v: v))
             setattr(self, name, setter(val))
         if self.is_mx_format:
-            raise NotImplementedError("modelopt_b200: MX (E8M0 block scale) formats are not implemented")
+            self._pass_through_bwd = True  # tensor_quantizer.py:289-290
 
     # ------------------------------------------------------------------ simple properties
     @property
@@ -422,7 +423,7 @@ class TensorQuantizer(nn.Module):
             if self.backend not in _QUANT_FUNCTIONAL_BACKENDS:
                 raise KeyError(f"Quant backend '{self.backend}' is not registered.")
             return _QUANT_FUNCTIONAL_BACKENDS[self.backend](inputs, self)
-        amax = self._get_amax(inputs)
+        amax = None if self.is_mx_format else self._get_amax(inputs)  # tensor_quantizer.py:898-900
         bs = self.block_sizes
         if bs is not None and bs.get("type", "static") == "dynamic":
             block_size = bs.get(-1, None) or bs.get(inputs.dim() - 1, None)
@@ -439,26 +440,58 @@ class TensorQuantizer(nn.Module):
                                  bs.get(-1) if bs else None,
                                  self.axis[0] if isinstance(self.axis, tuple) else self.axis)
 
-    def _real_quantize(self, inputs):
-        """tensor_quantizer.py:796-888, NVFP4 only: returns the packed tensor and keeps the scales."""
-        from ..qtensor import NVFP4QTensor, QTensorWrapper
+    def _is_real_quantize_support(self):
+        """tensor_quantizer.py:785-794."""
+        return bool((self._num_bits == 4 and self._block_sizes) or (self._num_bits == (2, 1) and self._block_sizes)
+                    or self._num_bits in ((4, 3), 8))
 
-        if not (self._num_bits == (2, 1) and self._block_sizes and self._block_sizes.get("scale_bits") == (4, 3)):
-            raise NotImplementedError("modelopt_b200: real quantization is implemented for NVFP4 only")
-        block = self._block_sizes.get(-1, None) or self._block_sizes.get(inputs.dim() - 1)
-        sf2 = None
-        if hasattr(self, "_amax"):
-            sf2 = (self._amax.float().amax() / (6.0 * 448.0)).to(inputs.device)
-        q, sf, sf2 = NVFP4QTensor.quantize(inputs, block, weights_scaling_factor_2=sf2)
-        self._set_buffer("_scale", sf)
-        self._set_buffer("_double_scale", sf2)
+    def _real_quantize(self, inputs):
+        """tensor_quantizer.py:796-888: returns the packed tensor and keeps the scales as buffers.  Every branch is one
+        packing kernel (csrc/pack_nvfp4.cu, csrc/pack_int.cu, csrc/qdq_mx.cu)."""
+        from ..qtensor import (FP8QTensor, INT4QTensor, INT8QTensor, MXFP4QTensor, MXFP8QTensor, NF4QTensor, NVFP4QTensor,
+                               QTensorWrapper)
+
+        assert self._is_real_quantize_support(), "Real quantization not supported for this format."
+        bs = self._block_sizes
+        buffers = {}
+        if bs and bs.get("scale_bits") == (8, 0) and bs.get("type") == "dynamic":
+            if self._num_bits == (2, 1):
+                q, buffers["_scale"] = MXFP4QTensor.quantize(inputs, bs[-1])
+            elif self._num_bits == (4, 3):
+                assert bs[-1] == MXFP8QTensor.BLOCK_SIZE, f"MXFP8 requires block size {MXFP8QTensor.BLOCK_SIZE}, got {bs[-1]}"
+                q, buffers["_scale"] = MXFP8QTensor.quantize(inputs)
+            else:
+                raise ValueError(f"Unsupported MX format: num_bits={self._num_bits}. "
+                                 "Expected (2, 1) for MXFP4 or (4, 3) for MXFP8.")
+        elif self._num_bits == (4, 3):
+            use_amax = self.amax is not None and not (bs and self.amax.numel() == 1)
+            q, buffers["_scale"] = FP8QTensor.quantize(inputs, axis=self._axis, block_sizes=bs,
+                                                      scales=ops.div_scalar(self.amax, 448.0) if use_amax else None)
+        elif self._num_bits == 8:
+            q, buffers["_scale"] = INT8QTensor.quantize(inputs, axis=self._axis, block_sizes=bs)
+        elif bs.get("scale_bits", 0) == 8 and bs.get("scale_block_sizes", None):
+            q, scales = NF4QTensor.quantize(inputs, bs[-1], bs["scale_block_sizes"][-1])
+            buffers["_scale"], buffers["_double_scale"], buffers["_scale_zeros"] = NF4QTensor.double_quantization(
+                scales, bs["scale_block_sizes"][-1], bs["scale_bits"])
+        elif bs.get("scale_bits") == (4, 3):
+            if bs.get("four_over_six", False):
+                raise NotImplementedError("NVFP4 Four-Over-Six (4/6) is not supported via mtq.compress")
+            block = bs.get(-1, None) or bs.get(inputs.dim() - 1)
+            sf2 = None
+            if hasattr(self, "_amax"):
+                sf2 = (self._amax.float().amax() / (6.0 * 448.0)).to(inputs.device)
+            q, buffers["_scale"], buffers["_double_scale"] = NVFP4QTensor.quantize(inputs, block, weights_scaling_factor_2=sf2)
+        else:
+            q, buffers["_scale"] = INT4QTensor.quantize(inputs, bs[-1])
+        for k, v in buffers.items():
+            self._set_buffer(k, v)
         self._dequantize = True
         return QTensorWrapper(q)
 
     def dequantize(self, inputs):
         q = inputs.get_qtensor() if hasattr(inputs, "get_qtensor") else inputs
         return q.dequantize(scale=self._scale, double_scale=getattr(self, "_double_scale", None),
-                            block_sizes=self.block_sizes)
+                            scale_zeros=getattr(self, "_scale_zeros", None), block_sizes=self.block_sizes)
 
     # ------------------------------------------------------------------ static block quantization: reshape
     def _block_sizes_to_axis(self, x):

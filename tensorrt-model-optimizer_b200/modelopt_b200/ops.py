@@ -495,6 +495,200 @@ def nvfp4_unpack(codes, sf, sf2, block, dtype, fast=False):
 
 
 # ------------------------------------------------------------------------------------------------
+# MX formats (csrc/qdq_mx.cu) and the integer / FP8 / NF4 packers (csrc/pack_int.cu)
+# ------------------------------------------------------------------------------------------------
+MX_FORMATS = {(4, 3): "E4M3", (5, 2): "E5M2", (3, 2): "E3M2", (2, 3): "E2M3", 8: "INT8", (8, 0): "E8M0",
+              (2, 1): "E2M1", (1, 2): "E1M2", (0, 3): "E0M3", (3, 0): "E3M0"}  # tensor_quant.py:30-41
+
+
+def qdq_mx(x, block, num_bits, scale_bits=(8, 0), global_amax=None, numerics=None, out=None):
+    """``fused_amax_convert``: dynamic block fake-quant of the last dim to an MX element format under E8M0 (or a
+    low-precision format's) block scales.  num_bits / scale_bits use the reference's (E, M) tuples or 8 for INT8."""
+    _cuda(x, "qdq_mx")
+    if x.dtype == torch.float64:
+        return _via_f32(qdq_mx, x, block, num_bits, scale_bits, global_amax, numerics)
+    if num_bits not in MX_FORMATS or num_bits == (8, 0) or scale_bits not in MX_FORMATS:
+        raise NotImplementedError(f"Unsupported num_bits: {num_bits}, scale_bits: {scale_bits} for dynamic block quantization.")
+    if int(block) not in (8, 16, 32):
+        raise ValueError("Blocksize for fused call must be one of {8, 16, 32}")
+    x = x.contiguous()
+    y = torch.empty_like(x) if out is None else out
+    cols = x.shape[-1] if x.dim() else 1
+    rows = x.numel() // max(cols, 1)
+    ga = None
+    if global_amax is not None and scale_bits != (8, 0):
+        ga = _f32_vec(global_amax.amax() if global_amax.numel() != 1 else global_amax, x)
+    with _dev(x):
+        _launched(_lib.load().mo_qdq_mx(x.data_ptr(), y.data_ptr(), rows, cols, _code(x), int(block),
+                                        _lib.MO_FMT[MX_FORMATS[num_bits]], _lib.MO_FMT[MX_FORMATS[scale_bits]],
+                                        None if ga is None else ga.data_ptr(), _mode(numerics), _stream(x)), "mo_qdq_mx")
+    return y
+
+
+def mxfp8_pack(x, sf=None, scales_only=False, numerics=None):
+    """x [..., N] -> (q float8_e4m3fn [..., N], sf uint8 [..., ceil(N/32)]); `sf` given: quantize with it."""
+    _cuda(x, "mxfp8_pack")
+    x = x.contiguous()
+    cols = x.shape[-1]
+    rows = x.numel() // max(cols, 1)
+    nb = (cols + 31) // 32
+    q = None if scales_only else torch.empty(x.shape, dtype=torch.float8_e4m3fn, device=x.device)
+    if sf is None:
+        sf_t = torch.empty((*x.shape[:-1], nb), dtype=torch.uint8, device=x.device)
+    else:
+        sf_t = sf.to(device=x.device).contiguous()
+        assert sf_t.dtype == torch.uint8 and sf_t.numel() == rows * nb
+    with _dev(x):
+        _launched(_lib.load().mo_mxfp8_pack(x.data_ptr(), None if q is None else q.data_ptr(), sf_t.data_ptr(), rows, cols,
+                                            _code(x), int(sf is not None), _mode(numerics), _stream(x)), "mo_mxfp8_pack")
+    return q, sf_t
+
+
+def mxfp4_pack(x, block=32, numerics=None):
+    """x (numel % block == 0) -> (codes uint8 [..., N/2], sf uint8 [numel/block, 1])."""
+    _cuda(x, "mxfp4_pack")
+    x = x.contiguous()
+    assert x.numel() % block == 0 and block % 2 == 0 and x.shape[-1] % 2 == 0
+    nb = x.numel() // block
+    q = torch.empty((*x.shape[:-1], x.shape[-1] // 2), dtype=torch.uint8, device=x.device)
+    sf = torch.empty((nb, 1), dtype=torch.uint8, device=x.device)
+    with _dev(x):
+        _launched(_lib.load().mo_mxfp4_pack(x.data_ptr(), q.data_ptr(), sf.data_ptr(), nb, int(block), _code(x),
+                                            _mode(numerics), _stream(x)), "mo_mxfp4_pack")
+    return q, sf
+
+
+def mx_unpack(q, sf, block, dtype, fp4=False):
+    """MXFP8 (q = e4m3 [..., N]) / MXFP4 (q = packed uint8 [..., N/2]) -> [..., N] `dtype`."""
+    _cuda(q, "mx_unpack")
+    q = q.contiguous()
+    sf = sf.to(q.device).contiguous()
+    cols = q.shape[-1] * (2 if fp4 else 1)
+    rows = q.numel() // max(q.shape[-1], 1)
+    assert sf.dtype == torch.uint8 and sf.numel() == rows * ((cols + block - 1) // block)
+    y = torch.empty((*q.shape[:-1], cols), dtype=dtype, device=q.device)
+    with _dev(q):
+        _launched(_lib.load().mo_mx_unpack(q.data_ptr(), sf.data_ptr(), y.data_ptr(), rows, cols, int(block), int(fp4),
+                                           _code(y), _stream(q)), "mo_mx_unpack")
+    return y
+
+
+def _pack4(fn, what, x, block, numerics):
+    _cuda(x, what)
+    x = x.contiguous()
+    assert x.numel() % block == 0 and block % 2 == 0
+    nb = x.numel() // block
+    scales = torch.empty((nb, 1), dtype=x.dtype, device=x.device)
+    q = torch.empty(x.numel() // 2, dtype=torch.uint8, device=x.device)
+    with _dev(x):
+        _launched(getattr(_lib.load(), fn)(x.data_ptr(), nb, int(block), _code(x), scales.data_ptr(), q.data_ptr(),
+                                           _mode(numerics), _stream(x)), fn)
+    return q, scales
+
+
+def int4_pack(x, block, numerics=None):
+    """flat x (numel % block == 0) -> (uint8 [numel/2], scales [numel/block, 1] = 7 / block amax in x.dtype)."""
+    return _pack4("mo_int4_pack", "int4_pack", x, block, numerics)
+
+
+def nf4_pack(x, block, numerics=None):
+    """flat x -> (uint8 [numel/2] NF4 indices, scales [numel/block, 1] = block amax in x.dtype)."""
+    return _pack4("mo_nf4_pack", "nf4_pack", x, block, numerics)
+
+
+def int4_unpack(q, scales, block):
+    _cuda(q, "int4_unpack")
+    q = q.contiguous().reshape(-1)
+    scales = scales.to(q.device).contiguous()
+    nb = q.numel() * 2 // block
+    assert scales.numel() == nb
+    y = torch.empty(q.numel() * 2, dtype=scales.dtype, device=q.device)
+    with _dev(q):
+        _launched(_lib.load().mo_int4_unpack(q.data_ptr(), scales.data_ptr(), nb, int(block), _code(scales), y.data_ptr(),
+                                             _stream(q)), "mo_int4_unpack")
+    return y
+
+
+def nf4_unpack(q, scales, block, bf16_form):
+    """scales: dequantized per-block scales (any float dtype).  bf16_form: the reference's CUDA kernel (bf16 out)."""
+    _cuda(q, "nf4_unpack")
+    q = q.contiguous().reshape(-1)
+    nb = q.numel() * 2 // block
+    assert scales.numel() == nb
+    out_dtype = torch.bfloat16 if (bf16_form or scales.dtype == torch.bfloat16) else torch.float32
+    s32 = _f32_vec(scales, q)
+    y = torch.empty(q.numel() * 2, dtype=out_dtype, device=q.device)
+    with _dev(q):
+        _launched(_lib.load().mo_nf4_unpack(q.data_ptr(), s32.data_ptr(), nb, int(block), _code(y), int(bool(bf16_form)),
+                                            y.data_ptr(), _stream(q)), "mo_nf4_unpack")
+    return y
+
+
+def _scale_map(shape, scale_shape):
+    """dims {O, A, I, bo, ba, bi, so, sa, si} for a tensor of `shape` whose scales (broadcast-shaped `scale_shape`,
+    same rank, each dim 1, the full size, or size / block) vary along at most three collapsed groups."""
+    shape, scale_shape = list(shape), list(scale_shape)
+    assert len(shape) == len(scale_shape), (shape, scale_shape)
+    # per dim: (size, block, n_scales)
+    dims = []
+    for n, m in zip(shape, scale_shape):
+        assert m >= 1 and n % m == 0, f"scale shape {scale_shape} does not tile {shape}"
+        dims.append((n, n // m, m))
+    # merge neighbouring dims that are both unscaled (m == 1) or both fully scaled (block == 1)
+    merged = []
+    for n, b, m in dims:
+        if n == 1:
+            continue
+        if merged and ((merged[-1][2] == 1 and m == 1) or (merged[-1][1] == 1 and b == 1)):
+            pn, pb, pm = merged[-1]
+            merged[-1] = (pn * n, pn * n if m == 1 else 1, pm * m)
+        else:
+            merged.append((n, b, m))
+    if len(merged) > 3:
+        raise NotImplementedError(f"modelopt_b200: scale layout {scale_shape} for {shape} needs more than 3 index groups")
+    while len(merged) < 3:
+        merged.insert(0, (1, 1, 1))
+    (o, bo, mo_), (a, ba, ma), (i, bi, mi) = merged
+    return [o, a, i, bo, ba, bi, ma * mi, mi, 1]
+
+
+def q8_pack(x, scales, kind):
+    """INT8 (kind 'int8') / FP8 E4M3 (kind 'fp8') codes of x / scales; scales broadcast-shaped like the reference's
+    (per-tensor, per-axis keepdims, or N-D blocks [.., n_i / block_i, ..])."""
+    _cuda(x, "q8_pack")
+    x = x.contiguous()
+    scales = scales.to(device=x.device, dtype=x.dtype).contiguous()
+    ss = list(scales.shape)
+    if scales.numel() == 1:
+        ss = [1] * x.dim()
+    elif len(ss) < x.dim():
+        ss = [1] * (x.dim() - len(ss)) + ss
+    dims = (C.c_int64 * 9)(*_scale_map(x.shape, ss))
+    q = torch.empty(x.shape, dtype=torch.int8 if kind == "int8" else torch.float8_e4m3fn, device=x.device)
+    with _dev(x):
+        _launched(_lib.load().mo_q8_pack(x.data_ptr(), q.data_ptr(), scales.data_ptr(), dims, _code(x),
+                                         0 if kind == "int8" else 1, _stream(x)), "mo_q8_pack")
+    return q
+
+
+def q8_unpack(q, scales, dtype, kind):
+    _cuda(q, "q8_unpack")
+    q = q.contiguous()
+    scales = scales.to(q.device).contiguous()
+    ss = list(scales.shape)
+    if scales.numel() == 1:
+        ss = [1] * q.dim()
+    elif len(ss) < q.dim():
+        ss = [1] * (q.dim() - len(ss)) + ss
+    dims = (C.c_int64 * 9)(*_scale_map(q.shape, ss))
+    y = torch.empty(q.shape, dtype=dtype, device=q.device)
+    with _dev(q):
+        _launched(_lib.load().mo_q8_unpack(q.data_ptr(), scales.data_ptr(), y.data_ptr(), dims, _code(scales), _code(y),
+                                           0 if kind == "int8" else 1, _stream(q)), "mo_q8_unpack")
+    return y
+
+
+# ------------------------------------------------------------------------------------------------
 # Scale searches (csrc/sweep.cu)
 # ------------------------------------------------------------------------------------------------
 def nvfp4_fp8_scale_sweep(x, global_amax, block_size=16, numerics=None):

@@ -55,13 +55,14 @@ def _dynamic_block_quantize_impl(inputs, block_size, amax, num_bits, exponent_bi
     """``tensorrt::dynamic_block_quantize_op`` (tensor_quant.py:157-195, :231-237)."""
     scale_bits = (scale_exponent_bits, scale_num_bits - scale_exponent_bits - 1)
     fmt = (exponent_bits, num_bits - exponent_bits - 1) if exponent_bits != 0 else num_bits
-    if fmt == (2, 1) and scale_bits == (4, 3):
-        assert amax is not None and amax.is_cuda, "amax must be a CUDA tensor for dynamic block quantization."
-        return ops.qdq_nvfp4_dynamic(inputs, amax, block_size)
-    raise NotImplementedError(
-        f"Unsupported num_bits: {fmt}, scale_bits: {scale_bits} for dynamic block quantization "
-        "(modelopt_b200 implements NVFP4: E2M1 values with E4M3 block scales)."
-    )
+    if fmt in ops.MX_FORMATS and fmt != (8, 0):
+        assert scale_bits in ops.MX_FORMATS, f"Scale bits should be in {ops.MX_FORMATS.keys()}"
+        if scale_bits != (8, 0):
+            assert amax is not None and amax.is_cuda, "amax must be a CUDA tensor for dynamic block quantization."
+        if fmt == (2, 1) and scale_bits == (4, 3) and amax is not None:
+            return ops.qdq_nvfp4_dynamic(inputs, amax, block_size)  # the reference's Triton fp4_fake_quant_block
+        return ops.qdq_mx(inputs, block_size, fmt, scale_bits, amax)  # cuda_ext_mx.fused_amax_convert
+    raise NotImplementedError(f"Unsupported num_bits: {fmt}, scale_bits: {scale_bits} for dynamic block quantization.")
 
 
 # ------------------------------------------------------------------------------------------------ op registration

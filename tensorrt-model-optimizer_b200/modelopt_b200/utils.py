@@ -38,6 +38,24 @@ def reduce_block_amax(input_tensor: torch.Tensor, block_sizes: dict) -> torch.Te
     return amax
 
 
+def reduce_block_padding(input: torch.Tensor, block_sizes: dict, pad_value: float = 0) -> torch.Tensor:
+    """core_utils.py:92-125: right-pad every blocked dim to a multiple of its block size."""
+    import torch.nn.functional as F
+
+    nd = input.dim()
+    pad = [0] * (2 * nd)
+    need = False
+    for dim, bs in block_sizes.items():
+        if not isinstance(dim, int):
+            continue
+        d = dim if dim >= 0 else nd + dim
+        rem = input.size(d) % bs
+        if rem:
+            pad[(nd - 1 - d) * 2 + 1] = bs - rem
+            need = True
+    return F.pad(input, pad, value=pad_value) if need else input
+
+
 def is_quantized(module) -> bool:
     from .nn.tensor_quantizer import TensorQuantizer
 

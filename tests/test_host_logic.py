@@ -100,9 +100,11 @@ def test_tensor_quantizer_attributes_and_state(mtq):
     q3.disable()
     x = torch.randn(3, 5)
     assert q3(x) is x  # disabled quantizer: identity, no compute (CPU tensor would raise otherwise)
-    with pytest.raises(NotImplementedError):
-        mtq.TensorQuantizer(mtq.QuantizerAttributeConfig(num_bits=(4, 3), block_sizes={-1: 32, "type": "dynamic",
-                                                                                          "scale_bits": (8, 0)}))
+    q4 = mtq.TensorQuantizer(mtq.QuantizerAttributeConfig(num_bits=(4, 3), block_sizes={-1: 32, "type": "dynamic",
+                                                                                             "scale_bits": (8, 0)}))
+    assert q4.is_mx_format and q4._pass_through_bwd and q4.amax is None  # tensor_quantizer.py:289-290, :360
+    q4._real_quantize  # noqa: B018  (exists; MXFP8 / MXFP4 / INT4 / INT8 / FP8 / NF4 packers are GPU-tested)
+    assert q4._is_real_quantize_support()
 
 
 def test_block_quant_reshape_bookkeeping(mtq):
