@@ -375,8 +375,19 @@ __global__ void __launch_bounds__(kThreads) mxfp8_pack_kernel(const T* __restric
   }
 }
 
-// One thread per 32-element block: codes = sign<<3 | #{bounds < |x / 2^e|}, two per byte, even element low
+// One thread per block: codes = sign<<3 | #{bounds < |x / 2^e|}, two per byte, even element low
 // (mxfp4_tensor.py:52-83).  Quirks kept: a zero element gets the sign bit ((2 - sign(0)) // 2 == 1), ties round DOWN.
+__device__ __forceinline__ uint32_t mxfp4_code(float v) {
+  const float a = fabsf(v);
+  const uint32_t ord = (a > 0.25f) + (a > 0.75f) + (a > 1.25f) + (a > 1.75f) + (a > 2.5f) + (a > 3.5f) + (a > 5.f);
+  return (v > 0.f ? 0u : 8u) | ord;
+}
+
+__device__ __forceinline__ float mxfp4_exponent(float amax, int gpu_div) {
+  const float descale = gpu_div ? __fmul_rn(amax, __frcp_rn(6.f)) : __fdiv_rn(amax, 6.f);
+  return ceilf(fmaxf(log2f(descale), -127.f));  // log2(0) = -inf -> -127
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kThreads) mxfp4_pack_kernel(const T* __restrict__ x, uint8_t* __restrict__ q,
                                                               uint8_t* __restrict__ sf, int64_t n_blocks, int block,
@@ -385,36 +396,114 @@ __global__ void __launch_bounds__(kThreads) mxfp4_pack_kernel(const T* __restric
     const T* xp = x + t * block;
     float m = 0.f;
     for (int i = 0; i < block; ++i) m = fmaxf(m, fabsf(Elem<T>::load(xp + i)));
-    const float descale = gpu_div ? __fmul_rn(m, __frcp_rn(6.f)) : __fdiv_rn(m, 6.f);
-    const float e = ceilf(fmaxf(log2f(descale), -127.f));  // log2(0) = -inf -> -127
-    const float div = exp2f(e);                            // exact: integer exponent
+    const float e = mxfp4_exponent(m, gpu_div);
+    const float div = exp2f(e);  // exact: integer exponent
     sf[t] = (uint8_t)(int)(e + 127.f);
     for (int i = 0; i < block; i += 2) {
-      uint32_t byte = 0;
-#pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const float v = __fdiv_rn(Elem<T>::load(xp + i + j), div);
-        const float a = fabsf(v);
-        const uint32_t ord = (a > 0.25f) + (a > 0.75f) + (a > 1.25f) + (a > 1.75f) + (a > 2.5f) + (a > 3.5f) + (a > 5.f);
-        const uint32_t code = (v > 0.f ? 0u : 8u) | ord;
-        byte |= code << (4 * j);
-      }
-      q[(t * block + i) >> 1] = (uint8_t)byte;
+      const uint32_t c0 = mxfp4_code(__fdiv_rn(Elem<T>::load(xp + i), div));
+      const uint32_t c1 = mxfp4_code(__fdiv_rn(Elem<T>::load(xp + i + 1), div));
+      q[(t * block + i) >> 1] = (uint8_t)(c0 | (c1 << 4));
     }
   }
 }
 
+// block == 32, aligned: the block lives in registers (NV 32-byte vectors), x / 2^e is the exact product x * 2^-e
+// (e in [-127, 126]), the 16 code bytes leave as one 16-byte store.
+template <typename T>
+__global__ void __launch_bounds__(kThreads) mxfp4_pack32_kernel(const T* __restrict__ x, uint8_t* __restrict__ q,
+                                                                uint8_t* __restrict__ sf, int64_t n_blocks, int gpu_div) {
+  constexpr int E = Elem<T>::kPerVec;
+  constexpr int NV = 32 / E;
+  const V32* xv = reinterpret_cast<const V32*>(x);
+  for (int64_t t = (int64_t)blockIdx.x * kThreads + threadIdx.x; t < n_blocks; t += (int64_t)gridDim.x * kThreads) {
+    float f[32];
+    V32 v[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) v[k] = ld_stream(xv + t * NV + k);
+#pragma unroll
+    for (int k = 0; k < NV; ++k) Elem<T>::unpack(v[k], f + k * E);
+    float m = fabsf(f[0]);
+#pragma unroll
+    for (int i = 1; i < 32; ++i) m = fmaxf(m, fabsf(f[i]));
+    const int e = (int)mxfp4_exponent(m, gpu_div);
+    sf[t] = (uint8_t)(e + 127);
+    const float mul = pow2i(-e);
+    // #{bounds < a} == the hardware's round-to-nearest-even E2M1 index, minus one at the three ties RNE sends up
+    // (0.75, 1.75, 3.5); one F2FP converts a pair.  (NaN elements: unspecified in the reference too.)
+    uint32_t w[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+      const float v0 = __fmul_rn(f[i], mul), v1 = __fmul_rn(f[i + 1], mul);
+      const float a = fabsf(v0), b = fabsf(v1);
+      uint32_t byte = e2m1_code2(a, b);
+      byte -= (a == 0.75f || a == 1.75f || a == 3.5f) ? 1u : 0u;
+      byte -= (b == 0.75f || b == 1.75f || b == 3.5f) ? 16u : 0u;
+      byte |= (v0 > 0.f ? 0u : 8u) | (v1 > 0.f ? 0u : 0x80u);
+      w[i / 8] |= byte << (8 * ((i % 8) / 2));
+    }
+    reinterpret_cast<uint4*>(q)[t] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
 // Dequantize: e4m3 codes (kind 0) or packed E2M1 nibbles (kind 1) times 2^(sf - 127), cast to T.
+// vec: a thread turns E codes into one 32-byte vector of outputs (cols % E == 0, block % E == 0).
 template <typename T>
 __global__ void __launch_bounds__(kThreads) mx_unpack_kernel(const uint8_t* __restrict__ q, const uint8_t* __restrict__ sf,
                                                              T* __restrict__ y, int64_t rows, int64_t cols, int block,
-                                                             int kind) {
+                                                             int kind, int vec) {
+  constexpr int E = Elem<T>::kPerVec;
   const int64_t bpr = (cols + block - 1) / block;
   const int64_t n = rows * cols;
+  if (vec) {
+    const int64_t nv = n / E;
+    const int64_t vpr = cols / E;
+    for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nv; i += (int64_t)gridDim.x * kThreads) {
+      const int64_t r = i / vpr, c = (i - r * vpr) * E;
+      const float mul = pow2i((int)sf[r * bpr + c / block] - 127);
+      float f[E];
+      if (kind == 0) {
+        uint32_t w[E / 4];
+        if constexpr (E == 16) {
+          const uint4 u = __ldg(reinterpret_cast<const uint4*>(q) + i);
+          w[0] = u.x; w[1] = u.y; w[2] = u.z; w[3] = u.w;
+        } else {
+          const uint2 u = __ldg(reinterpret_cast<const uint2*>(q) + i);
+          w[0] = u.x; w[1] = u.y;
+        }
+#pragma unroll
+        for (int k = 0; k < E; k += 2) {
+          uint32_t h2;
+          asm("cvt.rn.f16x2.e4m3x2 %0, %1;" : "=r"(h2) : "h"((uint16_t)((w[k / 4] >> (8 * (k % 4))) & 0xFFFFu)));
+          const float2 t = __half22float2(*reinterpret_cast<__half2*>(&h2));
+          f[k] = __fmul_rn(t.x, mul);
+          f[k + 1] = __fmul_rn(t.y, mul);
+        }
+      } else {
+        uint32_t w[E / 8];
+        if constexpr (E == 16) {
+          const uint2 u = __ldg(reinterpret_cast<const uint2*>(q) + i);
+          w[0] = u.x; w[1] = u.y;
+        } else {
+          w[0] = __ldg(reinterpret_cast<const uint32_t*>(q) + i);
+        }
+#pragma unroll
+        for (int k = 0; k < E; k += 2) {
+          uint32_t h2;
+          asm("{ .reg .b8 t; cvt.u8.u32 t, %1; cvt.rn.f16x2.e2m1x2 %0, t; }" : "=r"(h2) : "r"((w[k / 8] >> (4 * (k % 8))) & 0xFFu));
+          const float2 t = __half22float2(*reinterpret_cast<__half2*>(&h2));
+          f[k] = __fmul_rn(t.x, mul);
+          f[k + 1] = __fmul_rn(t.y, mul);
+        }
+      }
+      V32 o;
+      Elem<T>::pack(f, o);
+      st_stream(reinterpret_cast<V32*>(y) + i, o);
+    }
+    return;
+  }
   for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
     const int64_t r = i / cols, c = i % cols;
-    const int byte = sf[r * bpr + c / block];
-    const float mul = exp2f((float)byte - 127.f);
+    const float mul = pow2i((int)sf[r * bpr + c / block] - 127);
     float v;
     if (kind == 0) {
       uint32_t h2;
@@ -488,6 +577,15 @@ extern "C" int mo_mxfp4_pack(const void* x, uint8_t* q, uint8_t* sf, int64_t n_b
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int grid = persistent_grid((n_blocks + kThreads - 1) / kThreads, 8);
   const int gpu_div = numerics != MO_DIV_IEEE;
+  if (block == 32 && aligned32(x) && (reinterpret_cast<uintptr_t>(q) & 15u) == 0) {
+    switch (dtype) {
+      case MO_F32: mxfp4_pack32_kernel<float><<<grid, kThreads, 0, s>>>(static_cast<const float*>(x), q, sf, n_blocks, gpu_div); break;
+      case MO_F16: mxfp4_pack32_kernel<__half><<<grid, kThreads, 0, s>>>(static_cast<const __half*>(x), q, sf, n_blocks, gpu_div); break;
+      case MO_BF16: mxfp4_pack32_kernel<__nv_bfloat16><<<grid, kThreads, 0, s>>>(static_cast<const __nv_bfloat16*>(x), q, sf, n_blocks, gpu_div); break;
+      default: set_error("mo_mxfp4_pack: unsupported dtype %d", dtype); return MO_ERR_DTYPE;
+    }
+    return check_launch("mo_mxfp4_pack");
+  }
   switch (dtype) {
     case MO_F32: mxfp4_pack_kernel<float><<<grid, kThreads, 0, s>>>(static_cast<const float*>(x), q, sf, n_blocks, block, gpu_div); break;
     case MO_F16: mxfp4_pack_kernel<__half><<<grid, kThreads, 0, s>>>(static_cast<const __half*>(x), q, sf, n_blocks, block, gpu_div); break;
@@ -504,11 +602,13 @@ extern "C" int mo_mx_unpack(const uint8_t* q, const uint8_t* sf, void* y, int64_
   if (rows < 0 || cols < 0 || block < 1 || (kind != 0 && kind != 1)) { set_error("mo_mx_unpack: bad argument"); return MO_ERR_ARG; }
   if (kind == 1 && (cols & 1)) { set_error("mo_mx_unpack: packed E2M1 needs an even last dim"); return MO_ERR_SHAPE; }
   cudaStream_t s = static_cast<cudaStream_t>(stream);
-  const int grid = persistent_grid((rows * cols + kThreads - 1) / kThreads, 16);
+  const int ev = out_dtype == MO_F32 ? 8 : 16;
+  const int vec = cols % ev == 0 && block % ev == 0 && aligned32(y) && (reinterpret_cast<uintptr_t>(q) & 15u) == 0;
+  const int grid = persistent_grid(((vec ? rows * cols / ev : rows * cols) + kThreads - 1) / kThreads, 16);
   switch (out_dtype) {
-    case MO_F32: mx_unpack_kernel<float><<<grid, kThreads, 0, s>>>(q, sf, static_cast<float*>(y), rows, cols, block, kind); break;
-    case MO_F16: mx_unpack_kernel<__half><<<grid, kThreads, 0, s>>>(q, sf, static_cast<__half*>(y), rows, cols, block, kind); break;
-    case MO_BF16: mx_unpack_kernel<__nv_bfloat16><<<grid, kThreads, 0, s>>>(q, sf, static_cast<__nv_bfloat16*>(y), rows, cols, block, kind); break;
+    case MO_F32: mx_unpack_kernel<float><<<grid, kThreads, 0, s>>>(q, sf, static_cast<float*>(y), rows, cols, block, kind, vec); break;
+    case MO_F16: mx_unpack_kernel<__half><<<grid, kThreads, 0, s>>>(q, sf, static_cast<__half*>(y), rows, cols, block, kind, vec); break;
+    case MO_BF16: mx_unpack_kernel<__nv_bfloat16><<<grid, kThreads, 0, s>>>(q, sf, static_cast<__nv_bfloat16*>(y), rows, cols, block, kind, vec); break;
     default: set_error("mo_mx_unpack: unsupported dtype %d", out_dtype); return MO_ERR_DTYPE;
   }
   return check_launch("mo_mx_unpack");

@@ -56,7 +56,7 @@ def main():
     row("qdq_mx E2M1/E4M3 scales + global amax (generic kernel)",
         lambda: ops.qdq_mx(x, 16, (2, 1), (4, 3), x[0, :1].float().abs() + 8, out=y), 4 * n)
     row("torch copy (reference point)", lambda: y.copy_(x), 4 * n)
-    w = x[:8192]
+    w = x  # the whole 470 MB tensor: kernel times well above the Python launch overhead (~0.1 ms per call)
     nw = w.numel()
     row("mxfp8_pack (amax + E8M0 + e4m3 codes)", lambda: ops.mxfp8_pack(w), nw * (2 + 1 + 1 / 32))
     q8, s8 = ops.mxfp8_pack(w)
