@@ -94,6 +94,14 @@ int mo_qdq_nvfp4_dynamic(const void* x, void* y, int64_t rows, int64_t cols, int
 int mo_qdq_nvfp4_static(const void* x, void* y, int64_t n_blocks, int block, int in_dtype,
                         int out_dtype, const float* scale, int div_mode, void* stream);
 
+/* The two steps above in ONE launch: `amax` is the fp32 per-block amax, the scale is derived per thread
+ * (static_blockwise_fp4_fake_quant = compute_fp4_scales + the kernel, gemm/fp4_kernel.py:217-316).  Same dtype in and
+ * out, block in {16,32,64}, 32-byte aligned pointers; otherwise returns MO_ERR_ALIGN without launching and the caller
+ * uses mo_fp4_scales + mo_qdq_nvfp4_static.  global_amax is required when quantize_block_scales != 0. */
+int mo_qdq_nvfp4_static_amax(const void* x, void* y, int64_t n_blocks, int block, int dtype, const float* amax,
+                             const float* global_amax, int quantize_block_scales, float fp8_max_for_normalization,
+                             int div_mode, void* stream);
+
 /* Replaces compute_fp4_scales (gemm/fp4_kernel.py:217-251): scale = amax/6, optionally round-tripped
  * through E4M3 under scale_amax = global_amax*(448/fp8_max)/6.  global_amax == NULL: reduce it from
  * `amax` first (two launches).  amax/scale fp32 device arrays of n_blocks. */

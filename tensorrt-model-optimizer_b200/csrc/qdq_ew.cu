@@ -47,10 +47,16 @@ __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restric
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       const int64_t base = tile * tile_vecs + threadIdx.x;
       V32 v[kUnroll];
+      float am[kUnroll];  // per-channel / per-block amax fetched WITH the data, not after it arrived
+      const bool chunk = op.ax.mode == kPerChunk;
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
         const int64_t c = base + (int64_t)u * kThreads;
-        if (c < n_vec) v[u] = ld_stream(xv + c);
+        am[u] = 0.f;
+        if (c < n_vec) {
+          v[u] = ld_stream(xv + c);
+          if (chunk) am[u] = __ldg(op.ax.amax + op.ax.channel(c * E));
+        }
       }
 #pragma unroll
       for (int u = 0; u < kUnroll; ++u) {
@@ -69,7 +75,7 @@ __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restric
             Elem<T>::pack(f, v[u]);
             Elem<T>::unpack(v[u], f);
           }
-          op.template vec<E>(f, c * E);
+          op.template vec<E>(f, c * E, am[u], chunk);
           Elem<T>::pack(f, v[u]);
           st_stream(yv + c, v[u]);
         }

@@ -143,6 +143,31 @@ __global__ void __launch_bounds__(kThreads) nvfp4_dynamic_generic_kernel(const T
 // Static: per-block scale given.  Generic over (Tin, Tout, runtime block); vector fast path when
 // Tin == Tout, BLOCK in {16, 32, 64} and pointers are 32-byte aligned.
 // ------------------------------------------------------------------------------------------------
+// compute_fp4_scales (gemm/fp4_kernel.py:217-251): per-launch constants, then amax -> scale
+template <bool kIeee>
+struct Fp4ScaleOf {
+  float sc, inv;
+  bool quantize;
+  __device__ __forceinline__ Fp4ScaleOf(const float* global_amax, int q, float fp8_max) : sc(1.f), inv(1.f), quantize(q != 0) {
+    if (quantize) {
+      // scale_fp8_quant_amax = global_amax * (448 / fp8_max) / 6 ; then scaled_e4m3_impl(scale, that)
+      const float ga = __ldg(global_amax);
+      const float k = (float)(448.0 / (double)fp8_max);
+      float sa = __fmul_rn(ga, k);
+      sa = kIeee ? __fdiv_rn(sa, 6.0f) : __fmul_rn(sa, 1.0f / 6.0f);
+      const float safe = sa <= kEps ? 1.0f : sa;
+      // scaled_e4m3_impl: CUDA extension on the GPU (true division), `_fp8_eager` on CPU (reciprocal * 448)
+      sc = kIeee ? __fmul_rn(__fdiv_rn(1.0f, safe), 448.0f) : __fdiv_rn(448.0f, safe);
+      inv = __fdiv_rn(1.0f, sc);
+    }
+  }
+  __device__ __forceinline__ float operator()(float a) const {
+    float s = kIeee ? __fdiv_rn(a, 6.0f) : __fmul_rn(a, 1.0f / 6.0f);
+    if (quantize) s = __fmul_rn(e4m3_roundtrip1(__fmul_rn(s, sc)), inv);
+    return s;
+  }
+};
+
 struct StaticScale {
   float safe;
   bool zero;
@@ -152,11 +177,16 @@ struct StaticScale {
   }
 };
 
-template <typename T, int BLOCK, bool kIeee>
+// kFromAmax: `scale` holds the per-block AMAX and the scale is derived here (compute_fp4_scales folded in: no separate
+// pass that reads n_blocks amax values and writes n_blocks scales)
+template <typename T, int BLOCK, bool kIeee, bool kFromAmax>
 __global__ void __launch_bounds__(kThreads) nvfp4_static_kernel(const T* __restrict__ x, T* __restrict__ y,
-                                                                int64_t n_blocks, const float* __restrict__ scale) {
+                                                                int64_t n_blocks, const float* __restrict__ scale,
+                                                                const float* __restrict__ global_amax, int quantize,
+                                                                float fp8_max) {
   constexpr int E = Elem<T>::kPerVec;
   constexpr int NV = BLOCK / E;
+  const Fp4ScaleOf<kIeee> of(global_amax, kFromAmax ? quantize : 0, fp8_max);
   const V32* xv = reinterpret_cast<const V32*>(x);
   V32* yv = reinterpret_cast<V32*>(y);
   const int64_t tile_blocks = (int64_t)kThreads * kUnrollB;
@@ -181,7 +211,7 @@ __global__ void __launch_bounds__(kThreads) nvfp4_static_kernel(const T* __restr
         float f[BLOCK];
 #pragma unroll
         for (int k = 0; k < NV; ++k) Elem<T>::unpack(v[u][k], f + k * E);
-        const StaticScale ss(sc[u]);
+        const StaticScale ss(kFromAmax ? of(sc[u]) : sc[u]);
         qdq_block_values<BLOCK, kIeee>(f, ss.safe);
         if (ss.zero) {
 #pragma unroll
@@ -221,29 +251,13 @@ __global__ void __launch_bounds__(kThreads) fp4_cast_kernel(const Tin* __restric
   }
 }
 
-// compute_fp4_scales (gemm/fp4_kernel.py:217-251)
 template <bool kIeee>
 __global__ void __launch_bounds__(kThreads) fp4_scales_kernel(const float* __restrict__ amax, float* __restrict__ scale,
                                                               int64_t n, const float* __restrict__ global_amax,
                                                               int quantize, float fp8_max) {
-  float sc = 1.f, inv = 1.f;
-  if (quantize) {
-    // scale_fp8_quant_amax = global_amax * (448 / fp8_max) / 6 ; then scaled_e4m3_impl(scale, that)
-    const float ga = __ldg(global_amax);
-    const float k = (float)(448.0 / (double)fp8_max);
-    float sa = __fmul_rn(ga, k);
-    sa = kIeee ? __fdiv_rn(sa, 6.0f) : __fmul_rn(sa, 1.0f / 6.0f);
-    const float safe = sa <= kEps ? 1.0f : sa;
-    // scaled_e4m3_impl: CUDA extension on the GPU (true division), `_fp8_eager` on CPU (reciprocal * 448)
-    sc = kIeee ? __fmul_rn(__fdiv_rn(1.0f, safe), 448.0f) : __fdiv_rn(448.0f, safe);
-    inv = __fdiv_rn(1.0f, sc);
-  }
-  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads) {
-    const float a = amax[i];
-    float s = kIeee ? __fdiv_rn(a, 6.0f) : __fmul_rn(a, 1.0f / 6.0f);
-    if (quantize) s = __fmul_rn(e4m3_roundtrip1(__fmul_rn(s, sc)), inv);
-    scale[i] = s;
-  }
+  const Fp4ScaleOf<kIeee> of(global_amax, quantize, fp8_max);
+  for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
+    scale[i] = of(amax[i]);
 }
 
 __global__ void __launch_bounds__(kThreads) absmax_f32_kernel(const float* __restrict__ a, int64_t n, uint32_t* out) {
@@ -278,21 +292,29 @@ static int launch_dynamic(const void* x, void* y, int64_t rows, int64_t cols, co
 }
 
 template <typename Tin, typename Tout, bool kIeee>
-static int launch_static(const void* x, void* y, int64_t nb, int block, const float* scale, cudaStream_t s) {
+static int launch_static(const void* x, void* y, int64_t nb, int block, const float* scale, cudaStream_t s,
+                         bool from_amax = false, const float* ga = nullptr, int quantize = 0, float fp8_max = 448.f) {
   const Tin* xp = static_cast<const Tin*>(x);
   Tout* yp = static_cast<Tout*>(y);
   if constexpr (std::is_same<Tin, Tout>::value) {
     constexpr int E = Elem<Tin>::kPerVec;
     if (aligned32(x) && aligned32(y) && (block == 16 || block == 32 || block == 64) && block % E == 0) {
       const int64_t tiles = (nb + (int64_t)kThreads * kUnrollB - 1) / ((int64_t)kThreads * kUnrollB);
-#define MO_STA(B) nvfp4_static_kernel<Tin, B, kIeee><<<resident_grid((const void*)nvfp4_static_kernel<Tin, B, kIeee>, tiles), kThreads, 0, s>>>(xp, yp, nb, scale)
-      if (block == 16) MO_STA(16);
-      else if (block == 32) MO_STA(32);
-      else MO_STA(64);
+#define MO_STA(B, F) nvfp4_static_kernel<Tin, B, kIeee, F><<<resident_grid((const void*)nvfp4_static_kernel<Tin, B, kIeee, F>, tiles), kThreads, 0, s>>>(xp, yp, nb, scale, ga, quantize, fp8_max)
+      if (from_amax) {
+        if (block == 16) MO_STA(16, true);
+        else if (block == 32) MO_STA(32, true);
+        else MO_STA(64, true);
+      } else {
+        if (block == 16) MO_STA(16, false);
+        else if (block == 32) MO_STA(32, false);
+        else MO_STA(64, false);
+      }
 #undef MO_STA
       return check_launch("mo_qdq_nvfp4_static");
     }
   }
+  if (from_amax) return MO_ERR_ALIGN;  // the caller falls back to mo_fp4_scales + the generic kernel
   const int grid = persistent_grid((nb * block + kThreads - 1) / kThreads, 8);
   nvfp4_static_generic_kernel<Tin, Tout, kIeee><<<grid, kThreads, 0, s>>>(xp, yp, nb, block, scale);
   return check_launch("mo_qdq_nvfp4_static(generic)");
@@ -403,4 +425,35 @@ extern "C" int mo_fp4_scales(const float* amax, float* scale, int64_t n_blocks, 
     fp4_scales_kernel<false><<<grid, kThreads, 0, s>>>(amax, scale, n_blocks, global_amax, quantize_block_scales,
                                                        fp8_max_for_normalization);
   return check_launch("mo_fp4_scales");
+}
+
+// Fused form: per-block amax in, scale derived in the kernel (one launch instead of mo_fp4_scales + mo_qdq_nvfp4_static).
+// Returns MO_ERR_ALIGN (without launching) when the vector path does not apply: the caller uses the two-call form.
+template <typename T>
+static int static_amax_dispatch(const void* x, void* y, int64_t nb, int block, const float* amax, const float* ga, int q,
+                                float fp8_max, bool ieee, cudaStream_t s) {
+  return ieee ? launch_static<T, T, true>(x, y, nb, block, amax, s, true, ga, q, fp8_max)
+              : launch_static<T, T, false>(x, y, nb, block, amax, s, true, ga, q, fp8_max);
+}
+
+extern "C" int mo_qdq_nvfp4_static_amax(const void* x, void* y, int64_t n_blocks, int block, int dtype, const float* amax,
+                                        const float* global_amax, int quantize_block_scales,
+                                        float fp8_max_for_normalization, int div_mode, void* stream) {
+  if (n_blocks == 0) return MO_OK;
+  if (!x || !y || !amax || (quantize_block_scales && !global_amax)) {
+    set_error("mo_qdq_nvfp4_static_amax: NULL pointer");
+    return MO_ERR_NULL;
+  }
+  if (block != 16 && block != 32 && block != 64) return MO_ERR_ALIGN;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const bool ieee = div_mode == MO_DIV_IEEE;
+  int rc;
+  switch (dtype) {
+    case MO_F32: rc = static_amax_dispatch<float>(x, y, n_blocks, block, amax, global_amax, quantize_block_scales, fp8_max_for_normalization, ieee, s); break;
+    case MO_F16: rc = static_amax_dispatch<__half>(x, y, n_blocks, block, amax, global_amax, quantize_block_scales, fp8_max_for_normalization, ieee, s); break;
+    case MO_BF16: rc = static_amax_dispatch<__nv_bfloat16>(x, y, n_blocks, block, amax, global_amax, quantize_block_scales, fp8_max_for_normalization, ieee, s); break;
+    default: set_error("mo_qdq_nvfp4_static_amax: unsupported dtype %d", dtype); return MO_ERR_DTYPE;
+  }
+  if (rc == MO_ERR_ALIGN) set_error("mo_qdq_nvfp4_static_amax: vector path not applicable (alignment / block)");
+  return rc;
 }

@@ -70,9 +70,10 @@ struct Fp8Op {
     a = __fmul_rn(p, inv);
     b = __fmul_rn(q, inv);
   }
+  // am: the chunk's amax when the caller prefetched it with the data (kPerChunk), else ignored
   template <int N>
-  __device__ __forceinline__ void vec(float* f, int64_t idx0) {
-    if (ax.mode == kPerChunk) set(__ldg(ax.amax + ax.channel(idx0)));
+  __device__ __forceinline__ void vec(float* f, int64_t idx0, float am, bool have_am) {
+    if (ax.mode == kPerChunk) set(have_am ? am : __ldg(ax.amax + ax.channel(idx0)));
     if (ax.mode == kPerElem) {
 #pragma unroll
       for (int i = 0; i < N; ++i) f[i] = one(f[i], idx0 + i);
@@ -81,6 +82,8 @@ struct Fp8Op {
 #pragma unroll
     for (int i = 0; i < N; i += 2) pair(f[i], f[i + 1]);
   }
+  template <int N>
+  __device__ __forceinline__ void vec(float* f, int64_t idx0) { vec<N>(f, idx0, 0.f, false); }
   __device__ __forceinline__ float one(float v, int64_t idx) {
     if (ax.mode != kPerTensor) set(__ldg(ax.amax + ax.channel(idx)));
     float z = 0.f;
@@ -149,8 +152,10 @@ struct IntOp {
   }
   __device__ __forceinline__ float q1(float x) { return dfast ? q1t<true>(x) : q1t<false>(x); }
   template <int N>
-  __device__ __forceinline__ void vec(float* f, int64_t idx0) {
-    if (ax.mode == kPerChunk) set(__ldg(ax.amax + ax.channel(idx0)));
+  __device__ __forceinline__ void vec(float* f, int64_t idx0) { vec<N>(f, idx0, 0.f, false); }
+  template <int N>
+  __device__ __forceinline__ void vec(float* f, int64_t idx0, float am, bool have_am) {
+    if (ax.mode == kPerChunk) set(have_am ? am : __ldg(ax.amax + ax.channel(idx0)));
     if (ax.mode == kPerElem) {
 #pragma unroll
       for (int i = 0; i < N; ++i) f[i] = one(f[i], idx0 + i);

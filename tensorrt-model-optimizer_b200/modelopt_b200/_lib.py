@@ -17,6 +17,7 @@ MO_DIV_TRITON, MO_DIV_IEEE = MO_NUMERICS_GPU, MO_NUMERICS_CPU
 MO_FLAG_NEGATIVE_IN_UNSIGNED, MO_FLAG_NEGATIVE_AMAX = 1, 2
 # element / scale formats (the reference's `Types` enum order, gemm/tensor_quant_mx.h:39)
 MO_FMT = {"E4M3": 0, "E5M2": 1, "INT8": 2, "E0M3": 3, "E1M2": 4, "E3M0": 5, "E2M1": 6, "E3M2": 7, "E2M3": 8, "E8M0": 9}
+MO_ERR_ALIGN = -5
 ABI_VERSION = 3
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
@@ -29,6 +30,7 @@ SIGNATURES = {
     "mo_qdq_fp8": [_p, _p, _i64, _i, _p, _i64, _i64, _i, _p],
     "mo_qdq_nvfp4_dynamic": [_p, _p, _i64, _i64, _i, _p, _i, _i, _p],
     "mo_qdq_nvfp4_static": [_p, _p, _i64, _i, _i, _i, _p, _i, _p],
+    "mo_qdq_nvfp4_static_amax": [_p, _p, _i64, _i, _i, _p, _p, _i, _f, _i, _p],
     "mo_fp4_scales": [_p, _p, _i64, _p, _i, _f, _i, _p, _p],
     "mo_fp4_cast": [_p, _p, _i64, _i, _i, _p],
     "mo_amax": [_p, _i64, _i64, _i64, _i, _p, _p],

@@ -228,9 +228,22 @@ def qdq_nvfp4_static(x, amax, global_amax=None, quantize_block_scales=True, fp8_
         )
     block = x.numel() // nb
     out_dtype = out_dtype or x.dtype
-    scale = fp4_scales(amax, global_amax, quantize_block_scales, fp8_max_for_normalization, numerics)
     x = x.contiguous()
     y = torch.empty(x.shape, dtype=out_dtype, device=x.device)
+    if (out_dtype == x.dtype and block in (16, 32, 64) and x.data_ptr() % 32 == 0
+            and (global_amax is not None or not quantize_block_scales)):
+        # one launch: the block scale is derived from the block amax inside the QDQ kernel
+        am = _f32_vec(amax, x)
+        ga = _f32_vec(global_amax, x) if global_amax is not None else None
+        with _dev(x):
+            rc = _lib.load().mo_qdq_nvfp4_static_amax(x.data_ptr(), y.data_ptr(), nb, block, _code(x), am.data_ptr(),
+                                                      ga.data_ptr() if ga is not None else None,
+                                                      int(bool(quantize_block_scales)), float(fp8_max_for_normalization),
+                                                      _mode(numerics), _stream(x))
+        if rc != _lib.MO_ERR_ALIGN:
+            _launched(rc, "mo_qdq_nvfp4_static_amax")
+            return y
+    scale = fp4_scales(amax, global_amax, quantize_block_scales, fp8_max_for_normalization, numerics)
     with _dev(x):
         _launched(_lib.load().mo_qdq_nvfp4_static(x.data_ptr(), y.data_ptr(), nb, block, _code(x), _code(y),
                                               scale.data_ptr(), _mode(numerics), _stream(x)), "mo_qdq_nvfp4_static")
