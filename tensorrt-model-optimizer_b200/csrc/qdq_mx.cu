@@ -223,9 +223,15 @@ __global__ void __launch_bounds__(kThreads) mx_e8m0_kernel(const T* __restrict__
         float f[BLOCK];
 #pragma unroll
         for (int k = 0; k < NV; ++k) Elem<T>::unpack(v[u][k], f + k * E);
-        float m = fabsf(f[0]);
+        float t[BLOCK];  // balanced max tree (max is associative): no 31-deep dependent chain per block
 #pragma unroll
-        for (int i = 1; i < BLOCK; ++i) m = fmaxf(m, fabsf(f[i]));
+        for (int i = 0; i < BLOCK; ++i) t[i] = fabsf(f[i]);
+#pragma unroll
+        for (int w = BLOCK / 2; w >= 1; w /= 2) {
+#pragma unroll
+          for (int i = 0; i < w; ++i) t[i] = fmaxf(t[i], t[i + w]);
+        }
+        const float m = t[0];
         const BlockScale s = mx_scale_e8m0(m, dmax, fast != 0);
 #pragma unroll
         for (int i = 0; i < BLOCK; i += 2) mx_qdq2<FMT>(f[i], f[i + 1], s);

@@ -28,9 +28,9 @@ __device__ __forceinline__ float global_scale_from_amax(float ga) {
 }
 
 template <bool kIeee>
-__device__ __forceinline__ float block_scale(float bmax, float gs, float six_gs) {
-  // common/nvfp4_quant.py:121-125 and fp4_kernel_hopper.py:83-84
-  float t = div_mode<kIeee>(bmax, six_gs);
+__device__ __forceinline__ float block_scale(float bmax, float gs, float six_gs, const DivFull& dsix) {
+  // common/nvfp4_quant.py:121-125 and fp4_kernel_hopper.py:83-84; dsix = DivFull(six_gs), hoisted by the caller
+  float t = kIeee ? __fdiv_rn(bmax, six_gs) : dsix(bmax);
   t = fminf(t, 448.0f);  // min.f32: NaN operand dropped
   float s = __fmul_rn(gs, e4m3_roundtrip1(t));
   return s >= 1e-5f ? s : 1.0f;
@@ -39,26 +39,48 @@ __device__ __forceinline__ float block_scale(float bmax, float gs, float six_gs)
 // Quantize-dequantize N values that share `s`; f in/out (fp32).
 template <int N, bool kIeee>
 __device__ __forceinline__ void qdq_block_values(float* f, float s) {
-  const DivSeq2 dv(s);  // IEEE mode: the division's own instruction sequence, reciprocal hoisted, packed fp32
+  if constexpr (kIeee) {
+    const DivSeq2 dv(s);  // the division's own instruction sequence, reciprocal hoisted, packed fp32
 #pragma unroll
-  for (int i = 0; i < N; i += 2) {
-    float a = fabsf(f[i]), b = fabsf(f[i + 1]);
-    if (kIeee && dv.ok) dv(a, b);
-    else { a = div_mode<kIeee>(a, s); b = div_mode<kIeee>(b, s); }
-    e2m1_roundtrip2(a, b);
-    const float oa = __fmul_rn(s, a), ob = __fmul_rn(s, b);
-    // reference: where(x >= 0, o, fma(-s, q, 0)); fma(-s,q,+0) == 0 - o (gives +0 for o == 0)
-    f[i] = f[i] >= 0.0f ? oa : __fsub_rn(0.0f, oa);
-    f[i + 1] = f[i + 1] >= 0.0f ? ob : __fsub_rn(0.0f, ob);
+    for (int i = 0; i < N; i += 2) {
+      float a = fabsf(f[i]), b = fabsf(f[i + 1]);
+      if (dv.ok) dv(a, b);
+      else { a = __fdiv_rn(a, s); b = __fdiv_rn(b, s); }
+      e2m1_roundtrip2(a, b);
+      const float oa = __fmul_rn(s, a), ob = __fmul_rn(s, b);
+      // reference: where(x >= 0, o, fma(-s, q, 0)); fma(-s,q,+0) == 0 - o (gives +0 for o == 0)
+      f[i] = f[i] >= 0.0f ? oa : __fsub_rn(0.0f, oa);
+      f[i + 1] = f[i + 1] >= 0.0f ? ob : __fsub_rn(0.0f, ob);
+    }
+  } else {
+    const DivFull df(s);  // div.full.f32 with the range test and MUFU.RCP once per block: one FMUL per quotient
+    const bool plain = df.plain();
+#pragma unroll
+    for (int i = 0; i < N; i += 2) {
+      float a = fabsf(f[i]), b = fabsf(f[i + 1]);
+      if (plain) { a = df.fast(a); b = df.fast(b); }
+      else { a = df(a); b = df(b); }
+      e2m1_roundtrip2(a, b);
+      const float oa = __fmul_rn(s, a), ob = __fmul_rn(s, b);
+      f[i] = f[i] >= 0.0f ? oa : __fsub_rn(0.0f, oa);
+      f[i + 1] = f[i + 1] >= 0.0f ? ob : __fsub_rn(0.0f, ob);
+    }
   }
 }
 
 template <int N>
 __device__ __forceinline__ float abs_max_drop_nan(const float* f) {
-  float m = fabsf(f[0]);
+  // max.f32 semantics (NaN dropped); a balanced tree instead of a 15-deep dependent chain (max is associative, so the
+  // result is the same): the chain's latency was exposed once per block
+  float m[N];
 #pragma unroll
-  for (int i = 1; i < N; ++i) m = fmaxf(m, fabsf(f[i]));  // max.f32 semantics
-  return m;
+  for (int i = 0; i < N; ++i) m[i] = fabsf(f[i]);
+#pragma unroll
+  for (int w = N / 2; w >= 1; w /= 2) {
+#pragma unroll
+    for (int i = 0; i < w; ++i) m[i] = fmaxf(m[i], m[i + w]);
+  }
+  return m[0];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -73,6 +95,7 @@ __global__ void __launch_bounds__(kThreads) nvfp4_dynamic_kernel(const T* __rest
   static_assert(NV >= 1 && BLOCK % E == 0, "block must be a whole number of 32-byte vectors");
   const float gs = global_scale_from_amax<kIeee>(__ldg(global_amax));
   const float six_gs = __fmul_rn(gs, 6.0f);
+  const DivFull dsix(six_gs);
   const V32* xv = reinterpret_cast<const V32*>(x);
   V32* yv = reinterpret_cast<V32*>(y);
   const int64_t tile_blocks = (int64_t)kThreads * kUnrollB;
@@ -95,7 +118,7 @@ __global__ void __launch_bounds__(kThreads) nvfp4_dynamic_kernel(const T* __rest
         float f[BLOCK];
 #pragma unroll
         for (int k = 0; k < NV; ++k) Elem<T>::unpack(v[u][k], f + k * E);
-        const float s = block_scale<kIeee>(abs_max_drop_nan<BLOCK>(f), gs, six_gs);
+        const float s = block_scale<kIeee>(abs_max_drop_nan<BLOCK>(f), gs, six_gs, dsix);
         qdq_block_values<BLOCK, kIeee>(f, s);
 #pragma unroll
         for (int k = 0; k < NV; ++k) {
@@ -120,6 +143,7 @@ __global__ void __launch_bounds__(kThreads) nvfp4_dynamic_generic_kernel(const T
                                                                          const float* __restrict__ global_amax) {
   const float gs = global_scale_from_amax<kIeee>(__ldg(global_amax));
   const float six_gs = __fmul_rn(gs, 6.0f);
+  const DivFull dsix(six_gs);
   const int64_t bpr = (cols + block - 1) / block;
   const int64_t total = rows * bpr;
   for (int64_t t = (int64_t)blockIdx.x * kThreads + threadIdx.x; t < total; t += (int64_t)gridDim.x * kThreads) {
@@ -130,7 +154,7 @@ __global__ void __launch_bounds__(kThreads) nvfp4_dynamic_generic_kernel(const T
     float m = fabsf(Elem<T>::load(xp));
     for (int i = 1; i < len; ++i) m = fmaxf(m, fabsf(Elem<T>::load(xp + i)));
     if (len < block) m = fmaxf(m, 0.0f);  // zero padding takes part in the max
-    const float s = block_scale<kIeee>(m, gs, six_gs);
+    const float s = block_scale<kIeee>(m, gs, six_gs, dsix);
     for (int i = 0; i < len; ++i) {
       float f[2] = {Elem<T>::load(xp + i), 0.0f};
       qdq_block_values<2, kIeee>(f, s);

@@ -27,6 +27,7 @@ __global__ void __launch_bounds__(kThreads) nvfp4_fp8_sweep_kernel(const T* __re
   constexpr int NV = BLOCK / E;
   __shared__ float s_scale[kNumFp8Cand];  // scale_safe per candidate
   __shared__ float s_cand[kNumFp8Cand];   // c_k = e4m3(k + 1) / 448
+  __shared__ float s_rcp[kNumFp8Cand], s_pre[kNumFp8Cand];  // div.full.f32's divisor-only part (DivFull), per candidate
   const float ga = __ldg(global_amax);
   for (int k = threadIdx.x; k < kNumFp8Cand; k += kThreads) {
     uint32_t h2;
@@ -37,6 +38,9 @@ __global__ void __launch_bounds__(kThreads) nvfp4_fp8_sweep_kernel(const T* __re
     s_cand[k] = c;
     const float sc = div_mode<kIeee>(__fmul_rn(c, ga), 6.0f);  // scale = c * global_amax / 6.0
     s_scale[k] = sc == 0.0f ? 1.0f : sc;
+    const DivFull df(s_scale[k]);
+    s_rcp[k] = df.r;
+    s_pre[k] = df.pre;
   }
   __syncthreads();
   const V32* xv = reinterpret_cast<const V32*>(x);
@@ -51,10 +55,14 @@ __global__ void __launch_bounds__(kThreads) nvfp4_fp8_sweep_kernel(const T* __re
 #pragma unroll 2
     for (int k = 0; k < kNumFp8Cand; ++k) {
       const float sc = s_scale[k];
+      const float rc = s_rcp[k], pre = s_pre[k];
       float part[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int i = 0; i < BLOCK; i += 2) {
-        float a = div_mode<kIeee>(w[i], sc), c = div_mode<kIeee>(w[i + 1], sc);
+        float a, c;
+        if constexpr (kIeee) { a = __fdiv_rn(w[i], sc); c = __fdiv_rn(w[i + 1], sc); }
+        else if (pre == 1.0f) { a = __fmul_rn(rc, w[i]); c = __fmul_rn(rc, w[i + 1]); }
+        else { a = __fmul_rn(rc, __fmul_rn(w[i], pre)); c = __fmul_rn(rc, __fmul_rn(w[i + 1], pre)); }
         e2m1_roundtrip2(a, c);  // fp4_round_magnitude
         const float d0 = __fsub_rn(w[i], __fmul_rn(a, sc));
         const float d1 = __fsub_rn(w[i + 1], __fmul_rn(c, sc));

@@ -18,6 +18,7 @@ from .config import *  # noqa: F401,F403
 from .conversion import *  # noqa: F401,F403
 from .model_calib import *  # noqa: F401,F403
 from .model_quant import *  # noqa: F401,F403
+from .compress import *  # noqa: F401,F403
 from .nn import (QuantModuleRegistry, TensorQuantizer, is_registered_quant_backend, register_quant_backend,  # noqa: F401
                  unregister_quant_backend)
 

@@ -254,7 +254,26 @@ class _QuantLinear(QuantLinearConvBase):
         self.__dict__["_w4_cache"] = (key, packed)
         return packed
 
+    def _forward_real_quant(self, input):
+        """Weight held packed (``mtq.compress``): dequantize with one kernel, then the tcgen05 GEMM (cuBLAS via
+        ``F.linear`` for operands it does not take).  Nothing is cached: the point of compress is the memory."""
+        from .. import ops
+
+        w = self.weight_quantizer(self._parameters["weight"])  # QTensorWrapper -> dequantize
+        x = self.input_quantizer(input)
+        if w.dtype != x.dtype:
+            w = w.to(x.dtype)
+        if (not torch.is_grad_enabled() or not (x.requires_grad or (self.bias is not None and self.bias.requires_grad))) \
+                and x.is_cuda and ops.linear_supported(x, w, self.bias):
+            out = ops.linear(x, w, self.bias)
+        else:
+            out = torch.nn.functional.linear(x, w, self.bias)
+        return self.output_quantizer(out)
+
     def forward(self, input, *args, **kwargs):
+        if hasattr(self._parameters.get("weight"), "get_qtensor") and not args and not kwargs \
+                and type(self)._original_cls.forward is nn.Linear.forward:
+            return self._forward_real_quant(input)
         if self._tcgen05_ok(input, args, kwargs):
             from .. import ops
 

@@ -448,8 +448,8 @@ class TensorQuantizer(nn.Module):
     def _real_quantize(self, inputs):
         """tensor_quantizer.py:796-888: returns the packed tensor and keeps the scales as buffers.  Every branch is one
         packing kernel (csrc/pack_nvfp4.cu, csrc/pack_int.cu, csrc/qdq_mx.cu)."""
-        from ..qtensor import (FP8QTensor, INT4QTensor, INT8QTensor, MXFP4QTensor, MXFP8QTensor, NF4QTensor, NVFP4QTensor,
-                               QTensorWrapper)
+        from ..qtensor import (FP8QTensor, INT4QTensor, INT8QTensor, MXFP4QTensor, MXFP8QTensor, NF4QTensor,
+                               NVFP4QTensor)
 
         assert self._is_real_quantize_support(), "Real quantization not supported for this format."
         bs = self._block_sizes
@@ -486,7 +486,7 @@ class TensorQuantizer(nn.Module):
         for k, v in buffers.items():
             self._set_buffer(k, v)
         self._dequantize = True
-        return QTensorWrapper(q)
+        return q  # a BaseQuantizedTensor; pack_real_quantize_weight wraps it into a QTensorWrapper parameter
 
     def dequantize(self, inputs):
         q = inputs.get_qtensor() if hasattr(inputs, "get_qtensor") else inputs

@@ -25,16 +25,33 @@ class BaseQuantizedTensor:
 
 
 class QTensorWrapper(torch.nn.Parameter):
-    """A Parameter that carries a quantized tensor through ``module.weight`` (base_qtensor.py)."""
+    """A Parameter that carries a quantized tensor through ``module.weight`` (base_qtensor.py:87-145): the payload is
+    the packed data, ``metadata`` keeps the original shape / dtype and the QTensor class."""
 
     def __new__(cls, qtensor, metadata=None):
         data = qtensor._quantized_data if isinstance(qtensor, BaseQuantizedTensor) else qtensor
         obj = torch.Tensor._make_subclass(cls, data, False)
-        obj._qtensor = qtensor
+        if metadata is None:
+            obj.metadata = dict(qtensor.metadata)
+            obj.metadata["qtensor_class"] = qtensor.__class__
+        else:
+            assert all(k in metadata for k in ("qtensor_class", "shape", "dtype")), f"metadata: {metadata}"
+            obj.metadata = metadata
         return obj
 
+    def dim(self):
+        return len(self.metadata["shape"])
+
+    def to(self, *args, **kwargs):
+        device, dtype, *_ = torch._C._nn._parse_to(*args, **kwargs)
+        data = self.data.to(device=device) if device else self.data
+        return QTensorWrapper(self.metadata["qtensor_class"](self.metadata["shape"], dtype or self.metadata["dtype"], data))
+
     def get_qtensor(self):
-        return self._qtensor
+        return self.metadata["qtensor_class"](self.metadata["shape"], self.metadata["dtype"], self.data)
+
+    def get_state(self):
+        return {"metadata": self.metadata, "quantized_data.shape": self.data.shape, "quantized_data.dtype": self.data.dtype}
 
 
 class NVFP4QTensor(BaseQuantizedTensor):

@@ -215,3 +215,42 @@ def test_full_size_round_trips(shape):
         q, sc = INT4QTensor.quantize(sl, 128)
         oq_q, oq_s = oq.int4_quantize(sl.cpu(), 128)
         assert torch.equal(q._quantized_data.cpu(), oq_q) and same(sc, oq_s)
+
+
+@pytest.mark.parametrize("preset,ratio,tol", [("INT4_BLOCKWISE_WEIGHT_ONLY_CFG", 0.3, 0.25), ("FP8_DEFAULT_CFG", 0.55, 0.08),
+                                               ("NVFP4_DEFAULT_CFG", 0.32, 0.3), ("INT8_DEFAULT_CFG", 0.55, 0.05),
+                                               ("MXFP8_DEFAULT_CFG", 0.55, 0.08), ("MXFP4_DEFAULT_CFG", 0.3, 0.3)])
+def test_compress_end_to_end(preset, ratio, tol):
+    """mtq.quantize -> mtq.compress (compress.py:179-222): weights become packed QTensorWrapper parameters (memory as
+    test_qtensor_cuda.py:57-64 checks), and the compressed forward equals the fake-quant forward to the rounding of the
+    dequantized weight."""
+    import modelopt_b200 as mtq
+    from modelopt_b200 import config as qcfg
+    from modelopt_b200.qtensor import QTensorWrapper
+
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(512, 1024), torch.nn.GELU(), torch.nn.Linear(1024, 512)).cuda().to(bf)
+    x = torch.randn(128, 512, device="cuda", dtype=bf)
+    mtq.quantize(model, getattr(qcfg, preset), lambda m: m(x))
+    with torch.no_grad():
+        fake = model(x)
+    before = sum(p.numel() * p.element_size() for p in model.parameters() if p.dim() == 2)
+    mtq.compress(model)
+    assert mtq.is_real_quantized(model)
+    for lin in (model[0], model[2]):
+        w = lin._parameters["weight"]
+        assert isinstance(w, QTensorWrapper) and w.metadata["shape"] == (lin.out_features, lin.in_features)
+        assert lin.weight_quantizer._dequantize and hasattr(lin.weight_quantizer, "_scale")
+    after = sum(p.numel() * p.element_size() for p in model.parameters() if isinstance(p, QTensorWrapper))
+    assert after / before <= ratio, (after, before)
+    with torch.no_grad():
+        real = model(x)
+    rel = (real.float() - fake.float()).norm() / fake.float().norm()
+    assert rel < tol, rel
+    # a partial config leaves the excluded layer fake-quantized
+    model2 = torch.nn.Sequential(torch.nn.Linear(512, 1024), torch.nn.GELU(), torch.nn.Linear(1024, 512)).cuda().to(bf)
+    mtq.quantize(model2, getattr(qcfg, preset), lambda m: m(x))
+    mtq.compress(model2, {"default": True, "*2.weight_quantizer": False})
+    assert isinstance(model2[0]._parameters["weight"], QTensorWrapper)
+    assert not isinstance(model2[2]._parameters["weight"], QTensorWrapper)
+    assert torch.isfinite(model2(x).float()).all()
