@@ -346,6 +346,24 @@ int mo_q8_unpack(const uint8_t* q, const void* scales, void* y, const int64_t* d
                  int kind, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Local-Hessian weight calibration.
+ * ---------------------------------------------------------------------------------------------- */
+/* Replaces _LocalHessianAccumulator.accumulate (model_calib.py:848-862): hessian[n] += X_n^T X_n for every block n of
+ * `block` (= 16) input columns, X = x viewed [tokens, cin] (any float dtype, products in fp32).  hessian: fp32
+ * [cin / 16, 16, 16], accumulated in place; scratch: mo_block_hessian_scratch_bytes(tokens, cin) bytes of device memory
+ * (partial sums of the token slices, added in a fixed order). */
+int64_t mo_block_hessian_scratch_bytes(int64_t tokens, int64_t cin);
+int mo_block_hessian(const void* x, int64_t tokens, int64_t cin, int dtype, int block, float* hessian, void* scratch,
+                     void* stream);
+/* Replaces Triton nvfp4_fp8_scale_sweep_hessian (gemm/nvfp4_fp8_sweep.py:173-290): w is [cout, n_cin_blocks * 16]
+ * row-major (block b = row * n_cin_blocks + n), hessian fp32 [n_cin_blocks, 16, 16] (normalised by the sample count by
+ * the caller); per block the candidate among the 126 FP8 scales (as quantised by compute_fp4_scales, :263-266) that
+ * minimises dw^T H dw, dw = w - quant(w); first minimum; best_amax[b] = candidate_amax[best] (fp32 [cout * n_cin_blocks]). */
+int mo_nvfp4_fp8_scale_sweep_hessian(const void* w, int64_t cout, int64_t n_cin_blocks, int block, int dtype,
+                                     const float* hessian, const float* global_amax, float* best_amax, int numerics,
+                                     void* stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.
  * ---------------------------------------------------------------------------------------------- */

@@ -142,6 +142,34 @@ def gen_qtensor(ext_main):
     return g
 
 
+def gen_hessian():
+    """Reference local-Hessian pieces on the GPU: `_LocalHessianAccumulator.accumulate` (model_calib.py:848-862) and the
+    Triton `nvfp4_fp8_scale_sweep_hessian` (gemm/nvfp4_fp8_sweep.py:236-290) + the 126-step Python sweep with the
+    error_func (calib/mse.py:286-299)."""
+    from modelopt.torch.kernels.quantization.gemm import nvfp4_fp8_scale_sweep_hessian
+    from modelopt.torch.quantization.model_calib import _LocalHessianAccumulator
+
+    g = {}
+    torch.manual_seed(99)
+    cout, cin = 192, 256
+    for dn, dt in DTYPES.items():
+        x1 = (torch.randn(300, cin) * (torch.rand(cin) * 2 + 0.1)).to(dt).cuda()
+        x2 = (torch.randn(77, cin) * 0.5).to(dt).cuda()
+        acc = _LocalHessianAccumulator(cout, cin, 16)
+        acc.accumulate(x1)
+        acc.accumulate(x2.reshape(7, 11, cin))
+        h = acc.normalized_hessian()
+        w = (torch.randn(cout, cin) * 0.05).to(dt).cuda()
+        w[3] = 0
+        w[5, :16] *= 30
+        ga = w.float().abs().amax()
+        best = nvfp4_fp8_scale_sweep_hessian(w.reshape(-1, 16), ga, h, block_size=16)
+        g[f"x1_{dn}"], g[f"x2_{dn}"], g[f"w_{dn}"] = to_np(x1), to_np(x2), to_np(w)
+        g[f"h_{dn}"], g[f"hraw_{dn}"], g[f"ga_{dn}"], g[f"best_{dn}"] = to_np(h), to_np(acc.hessian_per_block), to_np(ga), to_np(best)
+    np.savez_compressed(os.path.join(OUT, "hessian_b200.npz"), **g)
+    print("hessian_b200.npz:", len(g), "arrays")
+
+
 def compare_product(gm, gq):
     """For information: how the product kernels compare on the captured inputs (the tests assert this)."""
     from modelopt_b200 import ops
@@ -164,8 +192,12 @@ def compare_product(gm, gq):
 
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
+    if "--hessian-only" in sys.argv:
+        gen_hessian()
+        sys.exit(0)
     gm = gen_mx(load_ext("ext_mx", "modelopt_cuda_ext_mx"))
     gq = gen_qtensor(load_ext("ext_main", "modelopt_cuda_ext"))
+    gen_hessian()
     try:
         compare_product(gm, gq)
     except Exception as e:  # noqa: BLE001

@@ -167,31 +167,6 @@ __global__ void __launch_bounds__(kThreads) nvfp4_dynamic_generic_kernel(const T
 // Static: per-block scale given.  Generic over (Tin, Tout, runtime block); vector fast path when
 // Tin == Tout, BLOCK in {16, 32, 64} and pointers are 32-byte aligned.
 // ------------------------------------------------------------------------------------------------
-// compute_fp4_scales (gemm/fp4_kernel.py:217-251): per-launch constants, then amax -> scale
-template <bool kIeee>
-struct Fp4ScaleOf {
-  float sc, inv;
-  bool quantize;
-  __device__ __forceinline__ Fp4ScaleOf(const float* global_amax, int q, float fp8_max) : sc(1.f), inv(1.f), quantize(q != 0) {
-    if (quantize) {
-      // scale_fp8_quant_amax = global_amax * (448 / fp8_max) / 6 ; then scaled_e4m3_impl(scale, that)
-      const float ga = __ldg(global_amax);
-      const float k = (float)(448.0 / (double)fp8_max);
-      float sa = __fmul_rn(ga, k);
-      sa = kIeee ? __fdiv_rn(sa, 6.0f) : __fmul_rn(sa, 1.0f / 6.0f);
-      const float safe = sa <= kEps ? 1.0f : sa;
-      // scaled_e4m3_impl: CUDA extension on the GPU (true division), `_fp8_eager` on CPU (reciprocal * 448)
-      sc = kIeee ? __fmul_rn(__fdiv_rn(1.0f, safe), 448.0f) : __fdiv_rn(448.0f, safe);
-      inv = __fdiv_rn(1.0f, sc);
-    }
-  }
-  __device__ __forceinline__ float operator()(float a) const {
-    float s = kIeee ? __fdiv_rn(a, 6.0f) : __fmul_rn(a, 1.0f / 6.0f);
-    if (quantize) s = __fmul_rn(e4m3_roundtrip1(__fmul_rn(s, sc)), inv);
-    return s;
-  }
-};
-
 struct StaticScale {
   float safe;
   bool zero;

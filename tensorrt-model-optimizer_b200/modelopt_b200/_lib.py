@@ -67,6 +67,9 @@ SIGNATURES = {
     "mo_nf4_unpack": [_p, _p, _i64, _i, _i, _i, _p, _p],
     "mo_q8_pack": [_p, _p, _p, C.POINTER(_i64), _i, _i, _p],
     "mo_q8_unpack": [_p, _p, _p, C.POINTER(_i64), _i, _i, _i, _p],
+    "mo_block_hessian_scratch_bytes": [_i64, _i64],
+    "mo_block_hessian": [_p, _i64, _i64, _i, _i, _p, _p, _p],
+    "mo_nvfp4_fp8_scale_sweep_hessian": [_p, _i64, _i64, _i, _i, _p, _p, _p, _i, _p],
     "mo_selftest_e2m1": [C.POINTER(C.c_uint64)],
     "mo_selftest_exact_div": [_i, _i, C.c_uint64, C.POINTER(C.c_uint64)],
     "mo_qdq_fp8_host": [_p, _p, _i64, _i, _f, _i],

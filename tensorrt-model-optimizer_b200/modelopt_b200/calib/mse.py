@@ -129,8 +129,7 @@ class NVFP4MSECalibrator(MseCalibrator):
     def __init__(self, amax: torch.Tensor, global_amax: torch.Tensor, axis=None, quant_func: Callable | None = None,
                  error_func: Callable | None = None, hessian: torch.Tensor | None = None):
         super().__init__(amax=amax, axis=axis, quant_func=quant_func, error_func=error_func)
-        if hessian is not None:
-            raise NotImplementedError("modelopt_b200: the Hessian-weighted sweep is not implemented (SURVEY 8f rank 3)")
+        self._hessian = hessian  # [cin // block, block, block]: the Hessian-weighted sweep (local_hessian), mse.py:205-207
         self._global_amax = global_amax.to(dtype=torch.float32)
         self._best_amax = None
 
@@ -147,7 +146,12 @@ class NVFP4MSECalibrator(MseCalibrator):
         if self._best_amax is not None:
             raise RuntimeError("NVFP4MSECalibrator: a previous collect() call produced a final amax; "
                                "multi-collect is not supported. Call reset() to start a fresh cycle.")
-        if self._error_func is None and x.is_cuda and x.ndim == 2 and x.shape[0] == int(self._initial_amax.numel()):
+        blocked = x.is_cuda and x.ndim == 2 and x.shape[0] == int(self._initial_amax.numel())
+        if self._hessian is not None and blocked and x.shape[-1] == 16:  # wins over the plain path (mse.py:258-266)
+            best = ops.nvfp4_fp8_scale_sweep_hessian(x.detach(), self._global_amax, self._hessian, block_size=x.shape[-1])
+            self._best_amax = best.reshape(self._initial_amax.shape).to(torch.float32)
+            return
+        if self._error_func is None and blocked:
             best = ops.nvfp4_fp8_scale_sweep(x.detach(), self._global_amax, block_size=x.shape[-1])
             self._best_amax = best.reshape(self._initial_amax.shape).to(torch.float32)
             return

@@ -15,6 +15,7 @@ from collections.abc import Mapping, Sequence
 from typing import Any
 
 __all__ = ["QuantizerAttributeConfig", "normalize_quant_cfg_list", "INT8_DEFAULT_CFG", "INT8_SMOOTHQUANT_CFG",
+           "NVFP4_W4A4_WEIGHT_LOCAL_HESSIAN_CFG", "NVFP4_W4A4_WEIGHT_MSE_FP8_SWEEP_CFG",
            "MXFP8_DEFAULT_CFG", "MXFP6_DEFAULT_CFG", "MXFP4_DEFAULT_CFG", "MXINT8_DEFAULT_CFG", "W4A8_MXFP4_FP8_CFG",
            "FP8_DEFAULT_CFG", "NVFP4_DEFAULT_CFG", "INT4_AWQ_CFG", "INT4_BLOCKWISE_WEIGHT_ONLY_CFG",
            "NVFP4_AWQ_LITE_CFG", "W4A8_AWQ_BETA_CFG", "NVFP4_AWQ_CLIP_CFG", "NVFP4_AWQ_FULL_CFG", "choices"]
@@ -244,7 +245,14 @@ MXFP4_DEFAULT_CFG = _preset(_mx((2, 1)), _mx((2, 1)), None)
 MXINT8_DEFAULT_CFG = _preset(_mx(8), _mx(8), None)
 W4A8_MXFP4_FP8_CFG = _preset(_mx((2, 1)), {"num_bits": (4, 3), "axis": None}, None)
 
-choices = {"MXFP8_DEFAULT_CFG", "MXFP6_DEFAULT_CFG", "MXFP4_DEFAULT_CFG", "MXINT8_DEFAULT_CFG", "W4A8_MXFP4_FP8_CFG",
+# modelopt_recipes/configs/ptq/presets/model/nvfp4_w4a4_weight_local_hessian.yaml, nvfp4_w4a4_weight_mse_fp8_sweep.yaml
+_NVFP4_STATIC_W = {"num_bits": (2, 1), "block_sizes": {-1: 16, "type": "static", "scale_bits": (4, 3)}}
+NVFP4_W4A4_WEIGHT_LOCAL_HESSIAN_CFG = _preset(copy.deepcopy(_NVFP4_STATIC_W), copy.deepcopy(_NVFP4),
+                                              {"method": "local_hessian", "fp8_scale_sweep": True})
+NVFP4_W4A4_WEIGHT_MSE_FP8_SWEEP_CFG = _preset(copy.deepcopy(_NVFP4_STATIC_W), copy.deepcopy(_NVFP4),
+                                              {"method": "mse", "fp8_scale_sweep": True})
+
+choices = {"NVFP4_W4A4_WEIGHT_LOCAL_HESSIAN_CFG", "NVFP4_W4A4_WEIGHT_MSE_FP8_SWEEP_CFG", "MXFP8_DEFAULT_CFG", "MXFP6_DEFAULT_CFG", "MXFP4_DEFAULT_CFG", "MXINT8_DEFAULT_CFG", "W4A8_MXFP4_FP8_CFG",
            "INT8_DEFAULT_CFG", "INT8_SMOOTHQUANT_CFG", "FP8_DEFAULT_CFG", "NVFP4_DEFAULT_CFG", "INT4_AWQ_CFG",
            "INT4_BLOCKWISE_WEIGHT_ONLY_CFG", "NVFP4_AWQ_LITE_CFG", "W4A8_AWQ_BETA_CFG", "NVFP4_AWQ_CLIP_CFG",
            "NVFP4_AWQ_FULL_CFG"}

@@ -23,6 +23,7 @@ from .arena import AmaxArenaPool
 from .calib import MaxCalibrator
 from .nn.quant_module import QuantModule
 from .nn.tensor_quantizer import SequentialQuantizer, TensorQuantizer
+from .utils import is_quantized_linear
 
 __all__ = ["max_calibrate", "enable_stats_collection", "finish_stats_collection", "weight_only_quantize",
            "disable_pre_quant_scale_and_resmooth", "sync_histograms"]
@@ -190,13 +191,15 @@ def _mse_quant_func(x, amax, quantizer):
     return xq
 
 
-def _make_weight_mse_calibrator(q, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep):
-    """model_calib.py:664-730."""
+def _make_weight_mse_calibrator(q, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep, error_func=None,
+                                hessian=None):
+    """model_calib.py:664-730.  ``error_func`` / ``hessian``: the local-Hessian metric (closure for the generic sweep, raw
+    per-cin-block tensor for the fused NVFP4 kernel)."""
     from functools import partial
 
     from .calib import MseCalibrator, NVFP4MSECalibrator
 
-    if (not isinstance(q, TensorQuantizer) or not q.is_enabled or q._dynamic or q._calibrator is None
+    if (not isinstance(q, TensorQuantizer) or not q.is_enabled or q._dynamic or q.is_mx_format or q._calibrator is None
             or getattr(q, "_amax", None) is None):
         return None
     initial = q._amax.clone().detach()
@@ -204,30 +207,32 @@ def _make_weight_mse_calibrator(q, step_size, start_multiplier, stop_multiplier,
     quant_func = partial(_mse_quant_func, quantizer=q)
     if fp8_scale_sweep:
         if q.is_nvfp4_static and q.backend is None and getattr(q, "global_amax", None) is not None:
-            return NVFP4MSECalibrator(amax=initial, axis=axis, global_amax=q.global_amax, quant_func=quant_func)
+            return NVFP4MSECalibrator(amax=initial, axis=axis, global_amax=q.global_amax, quant_func=quant_func,
+                                      error_func=error_func, hessian=hessian)
         return None
     fused = None
-    if q.backend is None and q.pre_quant_scale is None and not q.is_nvfp4_static and not q.is_nvfp4_dynamic:
+    if (error_func is None and q.backend is None and q.pre_quant_scale is None and not q.is_nvfp4_static
+            and not q.is_nvfp4_dynamic):
         if isinstance(q._num_bits, int):
             fused = {"num_bits": q._num_bits, "unsigned": q._unsigned, "narrow_range": q._narrow_range}
         elif q._num_bits == (4, 3):
             fused = {"num_bits": (4, 3)}
     return MseCalibrator(amax=initial, axis=axis, step_size=step_size, start_multiplier=start_multiplier,
-                         stop_multiplier=stop_multiplier, quant_func=quant_func, fused=fused)
+                         stop_multiplier=stop_multiplier, quant_func=quant_func, error_func=error_func, fused=fused)
 
 
-@torch.no_grad()
-def mse_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, step_size: float = 0.1,
-                  start_multiplier: float = 0.25, stop_multiplier: float = 4.0, fp8_scale_sweep: bool = False, **_):
-    """model_calib.py:733-826: max-calibrate everything, then refine every weight amax by MSE search."""
-    max_calibrate(model, forward_loop, distributed_sync)
+def _mse_calibrate_weights(model, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep, error_func_for=None,
+                           hessian_for=None):
+    """model_calib.py:776-826: refine every eligible weight amax with its MSE (or Hessian-weighted) search."""
     seen = set()
     for module in model.modules():
         if id(module) in seen or not isinstance(module, QuantModule):
             continue
         seen.add(id(module))
         for weight, q in module.iter_weights_for_calibration():
-            cal = _make_weight_mse_calibrator(q, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep)
+            cal = _make_weight_mse_calibrator(q, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep,
+                                              error_func_for(q) if error_func_for else None,
+                                              hessian_for(q) if hessian_for else None)
             if cal is None:
                 continue
             old = q._calibrator
@@ -243,7 +248,124 @@ def mse_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, st
             q._calibrator = old
 
 
-__all__ += ["mse_calibrate"]
+@torch.no_grad()
+def mse_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, step_size: float = 0.1,
+                  start_multiplier: float = 0.25, stop_multiplier: float = 4.0, fp8_scale_sweep: bool = False, **_):
+    """model_calib.py:733-826: max-calibrate everything, then refine every weight amax by MSE search."""
+    max_calibrate(model, forward_loop, distributed_sync)
+    _mse_calibrate_weights(model, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep)
+
+
+class _LocalHessianAccumulator:
+    """model_calib.py:829-900: per-cin-block H = sum X^T X for one weight quantizer.  ``accumulate`` is ONE read of the
+    activation (mo_block_hessian) instead of float copy + transpose + reshape + batched matmul."""
+
+    def __init__(self, cout: int, cin: int, block_size: int):
+        self.cout, self.cin, self.block_size = cout, cin, block_size
+        self.num_blocks_per_cin = cin // block_size
+        self.is_enabled = cin % block_size == 0  # not block-divisible -> no Hessian (falls back to plain MSE)
+        self.hessian_per_block = None
+        self._normalized_hessian = None
+        self.num_samples = 0
+
+    @torch.no_grad()
+    def accumulate(self, input_tensor: torch.Tensor) -> None:
+        if not self.is_enabled:
+            return
+        from . import ops
+
+        x = input_tensor.reshape(-1, self.cin)
+        if self.hessian_per_block is None:
+            self.hessian_per_block = torch.zeros(self.num_blocks_per_cin, self.block_size, self.block_size,
+                                                 dtype=torch.float32, device=x.device)
+        if self.block_size == 16 and x.is_cuda and x.dtype in (torch.float32, torch.float16, torch.bfloat16):
+            ops.block_hessian_into(x, self.hessian_per_block, 16)
+        else:  # other block sizes: the reference's batched matmul
+            xt = x.to(torch.float32).T.reshape(self.num_blocks_per_cin, self.block_size, -1)
+            self.hessian_per_block += xt @ xt.transpose(-1, -2)
+        self.num_samples += input_tensor.numel() // self.cin
+
+    def normalized_hessian(self):
+        if self._normalized_hessian is None and self.hessian_per_block is not None and self.num_samples:
+            self._normalized_hessian = self.hessian_per_block / self.num_samples
+        return self._normalized_hessian
+
+    def build_error_func(self, keep_buffer: bool = False):
+        hessian = self.normalized_hessian()
+        if hessian is None:
+            return None
+        cout, bs = self.cout, self.block_size
+        if not keep_buffer:
+            self.hessian_per_block = None
+
+        def local_hessian_error(x, xq):
+            shape = x.shape
+            dw = (x - xq).view(cout, -1, bs)
+            loss = torch.einsum("cnb,nbd,cnd->cn", dw, hessian.to(dw.dtype), dw).reshape(-1)
+            return loss.unsqueeze(-1).expand(-1, bs).reshape(shape)
+
+        return local_hessian_error
+
+
+@torch.no_grad()
+def local_hessian_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, step_size: float = 0.1,
+                            start_multiplier: float = 0.25, stop_multiplier: float = 4.0, fp8_scale_sweep: bool = True,
+                            block_size: int = 16, debug: bool = False, **_):
+    """model_calib.py:1004-1125: max-calibrate, capture H = sum X^T X per weight from a forward with the weight quantizers
+    disabled, then run the weight search with dw^T H dw as the metric (static NVFP4 + fp8_scale_sweep: one fused kernel)."""
+    if forward_loop is None:
+        warnings.warn("forward_loop must be provided for local_hessian; skipping local_hessian")
+        return
+    max_calibrate(model, forward_loop, distributed_sync)
+    accumulators: dict[int, _LocalHessianAccumulator] = {}
+    handles = []
+
+    def dense_hook(linear, args):
+        if not args:
+            return
+        q = linear.weight_quantizer
+        w = linear._parameters["weight"]
+        acc = accumulators.get(id(q))
+        if acc is None:
+            acc = accumulators[id(q)] = _LocalHessianAccumulator(w.shape[0], w.shape[1], block_size)
+        x = args[0]
+        acc.accumulate(x.to_local() if hasattr(x, "to_local") else x)
+
+    disabled = []
+    for name, module in model.named_modules():
+        if is_quantized_linear(module) and isinstance(module.weight_quantizer, TensorQuantizer):
+            w = module._parameters.get("weight")
+            if w is None or w.dim() != 2 or not module.weight_quantizer.is_enabled:
+                continue
+            if w.shape[1] % block_size != 0:
+                warnings.warn(f"local_hessian: {name} input features ({w.shape[1]}) not divisible by block_size "
+                              f"({block_size}); falling back to plain MSE for these weights.")
+            handles.append(module.register_forward_pre_hook(dense_hook))
+    for module in model.modules():  # forward with weight fake-quant disabled; input quantizers untouched (:1069-1073)
+        q = getattr(module, "weight_quantizer", None)
+        for sub in (q if isinstance(q, SequentialQuantizer) else [q]):
+            if isinstance(sub, TensorQuantizer) and sub.is_enabled:
+                sub.disable()
+                disabled.append(sub)
+    try:
+        forward_loop(model)
+    finally:
+        for h in handles:
+            h.remove()
+        for sub in disabled:
+            sub.enable()
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+        warnings.warn("local_hessian: Hessian is not synced across ranks; refined weight amaxes may diverge under "
+                      "tensor/data parallelism. Treat local_hessian as single-rank for now.")
+    error_funcs = {qid: acc.build_error_func(keep_buffer=debug) for qid, acc in accumulators.items()}
+    hessians = {qid: acc.normalized_hessian() for qid, acc in accumulators.items()}
+    _mse_calibrate_weights(model, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep,
+                           error_func_for=lambda q: error_funcs.get(id(q)), hessian_for=lambda q: hessians.get(id(q)))
+    if debug:
+        model._local_hessian_accumulators = accumulators
+
+
+__all__ += ["mse_calibrate", "local_hessian_calibrate"]
 
 
 # =================================================================================================

@@ -26,6 +26,7 @@ def _algorithms() -> dict[str | None, Callable]:
     table: dict[str | None, Callable] = {"max": model_calib.max_calibrate}
     table["smoothquant"] = model_calib.smoothquant
     table["mse"] = model_calib.mse_calibrate
+    table["local_hessian"] = model_calib.local_hessian_calibrate
     for name in ("awq_lite", "awq_clip", "awq_full"):  # mode.py:236-238: every awq method goes through awq()
         table[name] = (lambda method: lambda model, forward_loop=None, **kw:
                        model_calib.awq(model, forward_loop, algorithm=method, **kw))(name)

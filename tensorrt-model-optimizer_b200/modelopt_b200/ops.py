@@ -722,6 +722,43 @@ def nvfp4_fp8_scale_sweep(x, global_amax, block_size=16, numerics=None):
     return best
 
 
+def block_hessian_into(x, hessian, block=16):
+    """hessian [cin/block, block, block] fp32 += per-block X^T X of x [..., cin] (one read of x)."""
+    _cuda(x, "block_hessian_into")
+    cin = x.shape[-1]
+    x = x.reshape(-1, cin).contiguous()
+    tokens = x.shape[0]
+    assert hessian.dtype == torch.float32 and hessian.is_contiguous() and hessian.shape == (cin // block, block, block)
+    lib = _lib.load()
+    scratch = torch.empty(max(int(lib.mo_block_hessian_scratch_bytes(tokens, cin)), 4), dtype=torch.uint8, device=x.device)
+    with _dev(x):
+        _launched(lib.mo_block_hessian(x.data_ptr(), tokens, cin, _code(x), int(block), hessian.data_ptr(),
+                                       scratch.data_ptr(), _stream(x)), "mo_block_hessian", 2)
+    return hessian
+
+
+def nvfp4_fp8_scale_sweep_hessian(x, global_amax, hessian, block_size=16, numerics=None):
+    """Per-block amax (fp32 [n_blocks]) whose FP8 scale minimises the Hessian-weighted NVFP4 error dw^T H dw; x is the
+    weight in the blocked [n_blocks, block] layout, row-major over (cout, cin // block)."""
+    _cuda(x, "nvfp4_fp8_scale_sweep_hessian")
+    if hessian.dim() != 3 or hessian.shape[1] != block_size or hessian.shape[2] != block_size:
+        raise ValueError(f"hessian must have shape [n_cin_blocks, {block_size}, {block_size}], got {tuple(hessian.shape)}.")
+    x = x.contiguous()
+    n_blocks = x.numel() // block_size
+    n_cin = hessian.shape[0]
+    if n_blocks % n_cin != 0:
+        raise ValueError(f"n_blocks ({n_blocks}) is not divisible by n_cin_blocks ({n_cin}).")
+    h = hessian.to(device=x.device, dtype=torch.float32).contiguous()
+    ga = _f32_vec(global_amax, x)
+    best = torch.empty(n_blocks, dtype=torch.float32, device=x.device)
+    with _dev(x):
+        _launched(_lib.load().mo_nvfp4_fp8_scale_sweep_hessian(x.data_ptr(), n_blocks // n_cin, n_cin, int(block_size),
+                                                               _code(x), h.data_ptr(), ga.data_ptr(), best.data_ptr(),
+                                                               _mode(numerics), _stream(x)),
+                  "mo_nvfp4_fp8_scale_sweep_hessian")
+    return best
+
+
 def mse_sweep_into(x, cand_amax, losses, num_bits=8, unsigned=False, narrow_range=False, numerics=None):
     """losses[k, a] += sum (x - fq(x, cand_amax[k, a]))^2.  `cand_amax` is [K] (per-tensor) or [K, *amax_shape] for a
     single-axis amax of `x`; `losses` is a float64 [K, axis_size] device tensor."""
