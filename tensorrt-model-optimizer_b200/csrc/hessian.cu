@@ -5,10 +5,10 @@
 // matmul - four passes over the activation) and the Triton `_fp8_scale_sweep_hessian_kernel`
 // (gemm/nvfp4_fp8_sweep.py:173-290: a [32, 16] x [16, 16] tl.dot per candidate).
 //
-// block_hessian_kernel: a CTA owns 256 input columns (16 blocks of 16) and a slice of the tokens; thread (n, i) keeps
-// row i of H_n in 16 registers; a 32-token tile is staged in shared memory as fp32 and every thread does 16 FMAs per
-// token from one conflict-free scalar read and four broadcast 16-byte reads.  The activation is read from HBM exactly
-// once (2 B per element); partial Hessians of the token slices are summed in a fixed order (deterministic).
+// block_hessian_kernel: a CTA owns 1024 input columns (64 blocks of 16) and a slice of the tokens; four threads share a
+// block, each keeping an 8x8 quarter of H_n in registers; an 8-token tile is staged in shared memory with 32-byte vector
+// copies.  The activation is read from HBM exactly once (2 B per element); partial Hessians of the token slices are
+// summed in a fixed order (deterministic).
 //
 // hessian_sweep_kernel: a CTA owns one cin-block and 256 output rows; H_n (1 KB) and the 126 candidate scales live in shared
 // memory, each thread keeps its 16 weights in registers and evaluates dw^T H dw for every candidate in fp32 FMAs
@@ -20,52 +20,86 @@
 namespace mo {
 
 constexpr int kHB = 16;          // Hessian block (NVFP4 block size)
-constexpr int kHCols = 256;      // input columns per CTA = kThreads
-constexpr int kHTok = 32;        // tokens per shared-memory tile
+constexpr int kHCols = 1024;     // input columns per CTA: 64 blocks of 16, four threads per block
+constexpr int kHTok = 8;         // tokens per shared-memory tile (8 x 1024 elements)
 constexpr int kNumCand = 126;    // positive finite E4M3 values (gemm/_fp8_scale_candidates.py:26-31)
 
+// Thread (n, qi, qj) of a CTA keeps the 8x8 quarter [8qi, 8qi+8) x [8qj, 8qj+8) of H_n in 64 registers: per token it reads
+// 8 + 8 values (two 16-byte shared-memory loads for bf16) and does 64 FMAs, so the FMA pipe, not the shared-memory port,
+// is the limit (the first version - one row of H_n per thread, 5 loads per 16 FMAs - ran at 10 % of the FMA rate).
 template <typename T>
 __global__ void __launch_bounds__(kThreads) block_hessian_kernel(const T* __restrict__ x, int64_t tokens, int64_t cin,
                                                                  int64_t tok_per_split, float* __restrict__ partial) {
-  __shared__ __align__(16) float tile[kHTok][kHCols];
+  constexpr int E = Elem<T>::kPerVec;                 // elements per 32-byte vector
+  constexpr int VPR = kHCols / E;                     // vectors per tile row
+  constexpr int LOADS = kHTok * VPR / kThreads;       // vectors per thread per tile
+  __shared__ __align__(32) T tile[kHTok][kHCols];     // raw elements: converted when read
   const int64_t col0 = (int64_t)blockIdx.x * kHCols;
   const int64_t t0 = (int64_t)blockIdx.y * tok_per_split;
   const int64_t t1 = min(tokens, t0 + tok_per_split);
   const int tid = threadIdx.x;
-  const int nb = tid >> 4;  // block within the CTA's 16
-  const bool col_ok = col0 + tid < cin;
-  float acc[kHB];
+  const int nb = tid >> 2, qi = (tid >> 1) & 1, qj = tid & 1;
+  const bool blk_ok = col0 + (int64_t)nb * kHB < cin;
+  float acc[8][8];
 #pragma unroll
-  for (int j = 0; j < kHB; ++j) acc[j] = 0.f;
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
   for (int64_t tb = t0; tb < t1; tb += kHTok) {
-    // stage: thread `tid` loads column col0 + tid of 32 tokens?  No - coalesce along the row: 256 threads cover one token
-    // row of 256 columns per step (512 contiguous bytes for bf16), 32 steps per tile
-#pragma unroll 8
-    for (int r = 0; r < kHTok; ++r) {
-      const int64_t t = tb + r;
-      tile[r][tid] = (t < t1 && col_ok) ? Elem<T>::load(x + t * cin + col0 + tid) : 0.f;
+#pragma unroll
+    for (int l = 0; l < LOADS; ++l) {
+      const int v = tid + l * kThreads, r = v / VPR, cv = v % VPR;
+      const int64_t t = tb + r, c = col0 + (int64_t)cv * E;
+      V32 d;
+      if (t < t1 && c < cin) d = ld_stream(reinterpret_cast<const V32*>(x + t * cin + c));
+      else {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) d.w[k] = 0u;
+      }
+      *reinterpret_cast<V32*>(&tile[r][cv * E]) = d;
     }
     __syncthreads();
-#pragma unroll 4
+#pragma unroll 2
     for (int r = 0; r < kHTok; ++r) {
-      const float a = tile[r][tid];
-      const float4* row = reinterpret_cast<const float4*>(&tile[r][nb * kHB]);
+      float a[8], b[8];
+      if constexpr (E == 16) {  // 8 elements = 16 bytes
+        const uint4 ua = *reinterpret_cast<const uint4*>(&tile[r][nb * kHB + 8 * qi]);
+        const uint4 ub = *reinterpret_cast<const uint4*>(&tile[r][nb * kHB + 8 * qj]);
+        const uint32_t wa[4] = {ua.x, ua.y, ua.z, ua.w}, wb[4] = {ub.x, ub.y, ub.z, ub.w};
 #pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const float4 v = row[q];
-        acc[4 * q + 0] = __fmaf_rn(a, v.x, acc[4 * q + 0]);
-        acc[4 * q + 1] = __fmaf_rn(a, v.y, acc[4 * q + 1]);
-        acc[4 * q + 2] = __fmaf_rn(a, v.z, acc[4 * q + 2]);
-        acc[4 * q + 3] = __fmaf_rn(a, v.w, acc[4 * q + 3]);
+        for (int k = 0; k < 4; ++k) {
+          if constexpr (std::is_same<T, __nv_bfloat16>::value) {
+            a[2 * k] = __uint_as_float(wa[k] << 16); a[2 * k + 1] = __uint_as_float(wa[k] & 0xffff0000u);
+            b[2 * k] = __uint_as_float(wb[k] << 16); b[2 * k + 1] = __uint_as_float(wb[k] & 0xffff0000u);
+          } else {
+            const float2 fa = __half22float2(*reinterpret_cast<const __half2*>(&wa[k]));
+            const float2 fb = __half22float2(*reinterpret_cast<const __half2*>(&wb[k]));
+            a[2 * k] = fa.x; a[2 * k + 1] = fa.y; b[2 * k] = fb.x; b[2 * k + 1] = fb.y;
+          }
+        }
+      } else {
+        const float4* pa = reinterpret_cast<const float4*>(&tile[r][nb * kHB + 8 * qi]);
+        const float4* pb = reinterpret_cast<const float4*>(&tile[r][nb * kHB + 8 * qj]);
+        const float4 a0 = pa[0], a1 = pa[1], b0 = pb[0], b1 = pb[1];
+        a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+        b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
       }
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = __fmaf_rn(a[i], b[j], acc[i][j]);
     }
     __syncthreads();
   }
-  if (col_ok) {
-    // partial[split][cin_block][i][j]; thread (nb, i = tid & 15)
-    float* out = partial + ((int64_t)blockIdx.y * (cin / kHB) + col0 / kHB + nb) * (kHB * kHB) + (tid & 15) * kHB;
+  if (blk_ok) {
+    // partial[split][cin_block][i][j]
+    float* out = partial + ((int64_t)blockIdx.y * (cin / kHB) + col0 / kHB + nb) * (kHB * kHB);
 #pragma unroll
-    for (int j = 0; j < kHB; j += 4) *reinterpret_cast<float4*>(out + j) = make_float4(acc[j], acc[j + 1], acc[j + 2], acc[j + 3]);
+    for (int i = 0; i < 8; ++i) {
+      float* row = out + (8 * qi + i) * kHB + 8 * qj;
+      *reinterpret_cast<float4*>(row) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+      *reinterpret_cast<float4*>(row + 4) = make_float4(acc[i][4], acc[i][5], acc[i][6], acc[i][7]);
+    }
   }
 }
 
@@ -177,7 +211,7 @@ extern "C" int mo_block_hessian(const void* x, int64_t tokens, int64_t cin, int 
                                 void* scratch, void* stream) {
   if (tokens == 0 || cin == 0) return MO_OK;
   if (!x || !hessian || !scratch) { set_error("mo_block_hessian: NULL pointer"); return MO_ERR_NULL; }
-  if (block != kHB || cin % kHB != 0 || tokens < 0) {
+  if (block != kHB || cin % kHB != 0 || tokens < 0 || !aligned32(x)) {
     set_error("mo_block_hessian: block must be 16 and cin a multiple of 16 (got block=%d, cin=%lld)", block, (long long)cin);
     return MO_ERR_ARG;
   }

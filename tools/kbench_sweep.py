@@ -49,8 +49,16 @@ def main():
 
             line(f"MseCalibrator {nm} per-row, fused (mo_mse_sweep)", fused)
             line(f"MseCalibrator {nm} per-row, 39 x (qdq + mse + sum) loop", loop, 3, 1)
+        cin = w.shape[1]
+        act = torch.randn(16384, cin, device="cuda", dtype=w.dtype)
+        hacc = torch.zeros(cin // 16, 16, 16, device="cuda")
+        line("block Hessian accumulate [16384, cin] (mo_block_hessian)", lambda: ops.block_hessian_into(act, hacc))
+        hn = hacc / 16384
+        line("Hessian-weighted fp8-scale sweep (mo_nvfp4_fp8_scale_sweep_hessian)",
+             lambda: ops.nvfp4_fp8_scale_sweep_hessian(xb, ga, hn))
+        del act
         ref = os.path.join(ROOT, "oracle", "_ref")
-        if os.path.isdir(os.path.join(ref, "modelopt")):
+        if os.path.isdir(os.path.join(ref, "modelopt")) and "--no-ref" not in sys.argv:
             sys.path[:0] = [ref, os.path.join(ROOT, "oracle", "ref_shims")]
             try:
                 import modelopt.torch.kernels.quantization.gemm as tk
@@ -69,6 +77,15 @@ def main():
 
                 line("REF python 126-step sweep", ref_py, 2, 1)
                 os.environ.pop("MODELOPT_NVFP4_TRITON_SWEEP", None)
+                # local-Hessian pieces: H = sum X^T X of a [16384, cin] activation, Hessian-weighted sweep
+                from modelopt.torch.quantization.model_calib import _LocalHessianAccumulator as RefAcc
+
+                cin = w.shape[1]
+                act = torch.randn(16384, cin, device="cuda", dtype=w.dtype)
+                racc = RefAcc(w.shape[0], cin, 16)
+                line("REF _LocalHessianAccumulator.accumulate [16384, cin]", lambda: racc.accumulate(act), 5, 2)
+                hh = racc.normalized_hessian()
+                line("REF triton nvfp4_fp8_scale_sweep_hessian", lambda: tk.nvfp4_fp8_scale_sweep_hessian(xb, ga, hh, 16))
             except Exception as e:  # noqa: BLE001
                 print("REF failed:", repr(e)[:300])
         del w, xb
