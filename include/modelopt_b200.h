@@ -363,6 +363,15 @@ int mo_nvfp4_fp8_scale_sweep_hessian(const void* w, int64_t cout, int64_t n_cin_
                                      const float* hessian, const float* global_amax, float* best_amax, int numerics,
                                      void* stream);
 
+/* Replaces Triton gptq_fused_block_scalar (gemm/gptq_fused_kernel.py:43-136): the GPTQ column loop of ONE block of
+ * `block` in {32,64,128,256} columns with the static NVFP4 quantizer fused in.  w: fp32 [rows, block] working weights of
+ * the block; qw / err (out): fp32 [rows, block] quantized weights and propagated errors; amax: fp32
+ * [rows, n_amax_blocks] per-block amax of the whole weight; global_scale = global_amax / (6 * 448); hinv: fp32
+ * [block, block] block of the upper Cholesky factor of the inverse Hessian; block_start: column offset of the block. */
+int mo_gptq_block_nvfp4(const float* w, float* qw, float* err, const float* amax, float global_scale, const float* hinv,
+                        int64_t rows, int block, int n_amax_blocks, int quant_block, int block_start, int numerics,
+                        void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).
  * Each returns the number of mismatching cases in *mismatches (host pointer), synchronously.

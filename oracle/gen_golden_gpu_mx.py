@@ -170,6 +170,35 @@ def gen_hessian():
     print("hessian_b200.npz:", len(g), "arrays")
 
 
+def gen_gptq():
+    """Reference fused GPTQ block kernel (Triton, gemm/gptq_fused_kernel.py) and the whole fused blockwise update
+    (utils/calib_utils.py:291-327) on the GPU."""
+    from modelopt.torch.kernels.quantization.gemm.gptq_fused_kernel import gptq_fused_block_scalar
+    from modelopt.torch.quantization.utils.calib_utils import (compute_hessian_inverse,
+                                                               gptq_blockwise_update_fused_scalar, update_hessian)
+
+    g = {}
+    torch.manual_seed(321)
+    rows, cin, blk = 96, 256, 128
+    w = (torch.randn(rows, cin) * 0.04).cuda()
+    w[:, 7] = 0  # dead input column
+    x = (torch.randn(700, cin) * (torch.rand(cin) * 2 + 0.2)).cuda()
+    hess, n = update_hessian(x[:400], torch.zeros(cin, cin, device="cuda"), 0)
+    hess, n = update_hessian(x[400:], hess, n)
+    h_inv = compute_hessian_inverse(hess, w, 0.01)
+    amax = w.view(rows, cin // 16, 16).abs().amax(-1)
+    gs = float(amax.max()) / (6.0 * 448.0)
+    qw, err = gptq_fused_block_scalar(w[:, :blk].clone().contiguous(), amax, gs, h_inv[:blk, :blk].contiguous(), 16, 0)
+    full = w.clone()
+    gptq_blockwise_update_fused_scalar(full, amax, gs, h_inv, blk, 16)
+    for k, v in (("w", w), ("x", x), ("hess", hess), ("h_inv", h_inv), ("amax", amax), ("qw", qw), ("err", err), ("full", full)):
+        g[k] = to_np(v)
+    g["gs"] = np.asarray(gs, dtype=np.float64)
+    g["n"] = np.asarray(n)
+    np.savez_compressed(os.path.join(OUT, "gptq_b200.npz"), **g)
+    print("gptq_b200.npz:", len(g), "arrays")
+
+
 def compare_product(gm, gq):
     """For information: how the product kernels compare on the captured inputs (the tests assert this)."""
     from modelopt_b200 import ops
@@ -195,9 +224,13 @@ if __name__ == "__main__":
     if "--hessian-only" in sys.argv:
         gen_hessian()
         sys.exit(0)
+    if "--gptq-only" in sys.argv:
+        gen_gptq()
+        sys.exit(0)
     gm = gen_mx(load_ext("ext_mx", "modelopt_cuda_ext_mx"))
     gq = gen_qtensor(load_ext("ext_main", "modelopt_cuda_ext"))
     gen_hessian()
+    gen_gptq()
     try:
         compare_product(gm, gq)
     except Exception as e:  # noqa: BLE001

@@ -41,3 +41,25 @@ def hessian_sweep(w: torch.Tensor, global_amax: torch.Tensor, hessian: torch.Ten
         losses.append(torch.einsum("cnb,nbd,cnd->cn", dw, h, dw).reshape(-1))
     losses = torch.stack(losses)
     return amax[losses.argmin(dim=0)], losses                # torch.argmin: first minimum
+
+
+def gptq_block_nvfp4(w_block, block_amax, global_scale, h_inv_blk, quant_block, block_start):
+    """Torch restatement of the Triton _gptq_scalar_kernel (gemm/gptq_fused_kernel.py:43-94) with IEEE divisions and an
+    unfused multiply-subtract (= the product's MO_NUMERICS_CPU).  Returns (qw, err), fp32 [rows, block]."""
+    w = w_block.detach().float().clone()
+    rows, bsz = w.shape
+    gs = torch.tensor(float(global_scale), dtype=torch.float32)
+    qw, err = torch.empty_like(w), torch.empty_like(w)
+    for col in range(bsz):
+        bam = block_amax[:, (block_start + col) // quant_block].float()
+        scale = torch.minimum(bam / (6.0 * gs), torch.tensor(448.0)).to(torch.float8_e4m3fn).float() * gs  # fp8_quantize_scale
+        zero = scale == 0
+        safe = torch.where(zero | torch.isnan(scale) | torch.isinf(scale), torch.ones_like(scale), scale)
+        ws = w[:, col]
+        q = e2m1_round_magnitude(ws.abs() / safe) * safe
+        q = torch.where(zero, torch.zeros_like(q), torch.where(ws >= 0, q, -q))
+        e = (ws - q) / h_inv_blk[col, col]
+        qw[:, col], err[:, col] = q, e
+        if col + 1 < bsz:
+            w[:, col + 1:] = w[:, col + 1:] - e[:, None] * h_inv_blk[col, col + 1:][None, :]
+    return qw, err

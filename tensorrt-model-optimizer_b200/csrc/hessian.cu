@@ -259,3 +259,95 @@ extern "C" int mo_nvfp4_fp8_scale_sweep_hessian(const void* w, int64_t cout, int
 #undef MO_HS
   return check_launch("mo_nvfp4_fp8_scale_sweep_hessian");
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// GPTQ column loop of one block, fused with the NVFP4 quantizer (replaces Triton _gptq_scalar_kernel,
+// gemm/gptq_fused_kernel.py:43-136; the reference runs one Triton program per row with masked [BLOCK] vector ops per
+// column).  One warp owns a row: lane l keeps columns l, l + 32, ... in registers; per column the owner's value is
+// broadcast by shuffle, every lane derives q and err = (w - q) / H^-1[c][c], and the lanes holding later columns apply
+// w_j -= err * H^-1[c][j].  Rows of the block's inverse-Hessian factor are read through L1 (all warps of a CTA walk
+// the same row at the same time).
+//   scale = e4m3(min(amax / (6 * gs), 448)) * gs          (common/nvfp4_quant.py:104-125)
+//   q     = sign(w) * e2m1(|w| / scale_safe) * scale_safe  (:66-101), zero scale -> 0
+// Numerics: GPU = Triton's `/` (div.full.f32) and fused multiply-subtract; CPU = IEEE division, separate multiply and
+// subtract (the torch restatement, oracle/hessian.py).
+// ---------------------------------------------------------------------------------------------------------------------
+namespace mo {
+
+template <int K, bool kIeee>
+__global__ void __launch_bounds__(kThreads) gptq_block_nvfp4_kernel(const float* __restrict__ w, float* __restrict__ qw,
+                                                                    float* __restrict__ err, const float* __restrict__ amax,
+                                                                    float gs, const float* __restrict__ hinv, int64_t rows,
+                                                                    int n_amax_blocks, int quant_block, int block_start) {
+  constexpr int B = 32 * K;
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+  if (row >= rows) return;  // whole warp
+  float wr[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) wr[k] = w[row * B + k * 32 + lane];
+  const float six_gs = __fmul_rn(6.0f, gs);
+  const float* arow = amax + row * n_amax_blocks;
+#pragma unroll
+  for (int kk = 0; kk < K; ++kk) {
+    for (int l = 0; l < 32; ++l) {
+      const int col = kk * 32 + l;
+      const float ws = __shfl_sync(0xffffffffu, wr[kk], l);
+      const float bam = __ldg(arow + (block_start + col) / quant_block);
+      // fp8_quantize_scale
+      float t = kIeee ? __fdiv_rn(bam, six_gs) : div_full(bam, six_gs);
+      t = fminf(t, 448.0f);
+      const float scale = __fmul_rn(e4m3_roundtrip1(t), gs);
+      // nvfp4_scalar_quant
+      const bool zero = scale == 0.0f;
+      const float safe = (zero || isnan(scale) || isinf(scale)) ? 1.0f : scale;
+      float a = kIeee ? __fdiv_rn(fabsf(ws), safe) : div_full(fabsf(ws), safe), z = 0.f;
+      e2m1_roundtrip2(a, z);
+      const float resc = __fmul_rn(a, safe);
+      const float q = zero ? 0.0f : (ws >= 0.0f ? resc : -resc);
+      const float d = __ldg(hinv + col * B + col);
+      const float diff = __fsub_rn(ws, q);
+      const float e = kIeee ? __fdiv_rn(diff, d) : div_full(diff, d);
+      if (lane == l) {
+        qw[row * B + col] = q;
+        err[row * B + col] = e;
+      }
+#pragma unroll
+      for (int k2 = 0; k2 < K; ++k2) {
+        const int j = k2 * 32 + lane;
+        if (j > col) {
+          const float h = __ldg(hinv + col * B + j);
+          wr[k2] = kIeee ? __fsub_rn(wr[k2], __fmul_rn(e, h)) : __fmaf_rn(-e, h, wr[k2]);
+        }
+      }
+    }
+  }
+}
+
+}  // namespace mo
+
+extern "C" int mo_gptq_block_nvfp4(const float* w, float* qw, float* err, const float* amax, float global_scale,
+                                   const float* hinv, int64_t rows, int block, int n_amax_blocks, int quant_block,
+                                   int block_start, int numerics, void* stream) {
+  if (rows == 0) return MO_OK;
+  if (!w || !qw || !err || !amax || !hinv) { set_error("mo_gptq_block_nvfp4: NULL pointer"); return MO_ERR_NULL; }
+  if (rows < 0 || quant_block < 1 || n_amax_blocks < 1 || block_start < 0 ||
+      (block != 32 && block != 64 && block != 128 && block != 256)) {
+    set_error("mo_gptq_block_nvfp4: block must be 32, 64, 128 or 256 (got %d)", block);
+    return MO_ERR_ARG;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int grid = (int)((rows + kThreads / 32 - 1) / (kThreads / 32));
+  const bool ieee = numerics == MO_DIV_IEEE;
+#define MO_GQ(KK)                                                                                                         \
+  if (ieee) mo::gptq_block_nvfp4_kernel<KK, true><<<grid, kThreads, 0, s>>>(w, qw, err, amax, global_scale, hinv, rows, n_amax_blocks, quant_block, block_start); \
+  else mo::gptq_block_nvfp4_kernel<KK, false><<<grid, kThreads, 0, s>>>(w, qw, err, amax, global_scale, hinv, rows, n_amax_blocks, quant_block, block_start)
+  switch (block) {
+    case 32: MO_GQ(1); break;
+    case 64: MO_GQ(2); break;
+    case 128: MO_GQ(4); break;
+    default: MO_GQ(8); break;
+  }
+#undef MO_GQ
+  return check_launch("mo_gptq_block_nvfp4");
+}

@@ -27,6 +27,9 @@ def _algorithms() -> dict[str | None, Callable]:
     table["smoothquant"] = model_calib.smoothquant
     table["mse"] = model_calib.mse_calibrate
     table["local_hessian"] = model_calib.local_hessian_calibrate
+    from . import gptq as _gptq
+
+    table["gptq"] = lambda model, forward_loop=None, **kw: _gptq.gptq(model, forward_loop, **kw)
     for name in ("awq_lite", "awq_clip", "awq_full"):  # mode.py:236-238: every awq method goes through awq()
         table[name] = (lambda method: lambda model, forward_loop=None, **kw:
                        model_calib.awq(model, forward_loop, algorithm=method, **kw))(name)

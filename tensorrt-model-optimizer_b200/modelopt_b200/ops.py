@@ -759,6 +759,23 @@ def nvfp4_fp8_scale_sweep_hessian(x, global_amax, hessian, block_size=16, numeri
     return best
 
 
+def gptq_block_nvfp4(w_block, block_amax, global_scale, h_inv_blk, quant_block_size, block_start, numerics=None):
+    """``gptq_fused_block_scalar``: (qw_block, err_block) of one GPTQ block, fp32 [rows, block]."""
+    _cuda(w_block, "gptq_block_nvfp4")
+    w_block = w_block.float().contiguous()
+    rows, block = w_block.shape
+    am = block_amax.to(device=w_block.device, dtype=torch.float32).contiguous()
+    h = h_inv_blk.to(device=w_block.device, dtype=torch.float32).contiguous()
+    assert h.shape == (block, block) and am.shape[0] == rows
+    qw, err = torch.empty_like(w_block), torch.empty_like(w_block)
+    with _dev(w_block):
+        _launched(_lib.load().mo_gptq_block_nvfp4(w_block.data_ptr(), qw.data_ptr(), err.data_ptr(), am.data_ptr(),
+                                                  float(global_scale), h.data_ptr(), rows, block, am.shape[1],
+                                                  int(quant_block_size), int(block_start), _mode(numerics),
+                                                  _stream(w_block)), "mo_gptq_block_nvfp4")
+    return qw, err
+
+
 def mse_sweep_into(x, cand_amax, losses, num_bits=8, unsigned=False, narrow_range=False, numerics=None):
     """losses[k, a] += sum (x - fq(x, cand_amax[k, a]))^2.  `cand_amax` is [K] (per-tensor) or [K, *amax_shape] for a
     single-axis amax of `x`; `losses` is a float64 [K, axis_size] device tensor."""
