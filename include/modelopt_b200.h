@@ -338,7 +338,9 @@ int mo_nf4_unpack(const uint8_t* q, const float* scales, int64_t n_blocks, int b
 /* Replaces INT8QTensor.quantize (kind 0, qtensor/int8_tensor.py:35-93) and FP8QTensor.quantize (kind 1,
  * qtensor/fp8_tensor.py:38-115) for per-tensor, per-axis and N-D block scales.  x is viewed [O, A, I]; element (o, a, i)
  * uses scales[(o / bo) * so + (a / ba) * sa + (i / bi) * si]; dims = {O, A, I, bo, ba, bi, so, sa, si} (host array).
- * scales have x's dtype.  q = int8(clamp(round(T(x / s)), -128, 127)) or e4m3(T(x / s)). */
+ * scales have x's dtype.  q = int8(clamp(round(T(x / s)), -128, 127)) or e4m3(T(x / s)); kind 2 = `_to_fp8`
+ * (backends/fp8_per_tensor_gemm.py:31-33, a compiled function): scales are FP32, the quotient stays in fp32, is clamped
+ * to +-448 (the saturating conversion) and converted to E4M3. */
 int mo_q8_pack(const void* x, uint8_t* q, const void* scales, const int64_t* dims, int dtype, int kind, void* stream);
 /* Replaces INT8QTensor.dequantize / FP8QTensor.dequantize (int8_tensor.py:95-124, fp8_tensor.py:117-151):
  * y = O(O(q) * O(scale)). */
@@ -371,6 +373,13 @@ int mo_nvfp4_fp8_scale_sweep_hessian(const void* w, int64_t cout, int64_t n_cin_
 int mo_gptq_block_nvfp4(const float* w, float* qw, float* err, const float* amax, float global_scale, const float* hinv,
                         int64_t rows, int block, int n_amax_blocks, int quant_block, int block_start, int numerics,
                         void* stream);
+
+/* Replaces the FP8 per-tensor real-quant GEMM backend (backends/fp8_per_tensor_gemm.py:36-50: torch._scaled_mm with
+ * per-tensor scale_a / scale_b): out[M,N] = (a[M,K] . b[N,K]^T) * scale_a * scale_b (+ bias), a / b = E4M3 codes
+ * (mo_q8_pack kind 2 = `(x / scale).clamp(-448, 448).to(e4m3)`, :31-33), scale_a / scale_b fp32 device scalars, bias and
+ * out in out_dtype (bf16 / f16).  tcgen05.mma.kind::f8f6f4, fp32 accumulation.  K % 16 == 0, N % 8 == 0. */
+int mo_linear_fp8(const uint8_t* a, const uint8_t* b, const float* scale_a, const float* scale_b, const void* bias,
+                  void* out, int64_t M, int64_t N, int64_t K, int out_dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Device self-tests of the numerics tricks the kernels rely on (run by the GPU test-suite).

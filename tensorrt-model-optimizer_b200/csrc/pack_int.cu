@@ -335,16 +335,26 @@ __device__ __forceinline__ uint32_t q8_code_of(float v) {  // v = T(x / s)
   if constexpr (KIND == 0) {
     if (v != v) return 0u;
     return (uint32_t)(int)fminf(fmaxf(rintf(v), -128.f), 127.f) & 0xFFu;
-  } else {
+  } else if constexpr (KIND == 1) {
     // torch's float8_e4m3fn cast does not saturate: anything that rounds past 448 (|v| > 464, inf, NaN) is NaN (0x7f)
     if (!(fabsf(v) <= 464.f)) return 0x7Fu | ((__float_as_uint(v) >> 24) & 0x80u);
+    return e4m3_code1(v);
+  } else {  // KIND 2: clamp(-448, 448) first (backends/fp8_per_tensor_gemm.py:31-33) = the saturating conversion
     return e4m3_code1(v);
   }
 }
 
+// KIND 2 (`_to_fp8` under torch.compile: the quotient stays in fp32, the scale is an fp32 tensor): no rounding to T
+template <typename T, int KIND>
+__device__ __forceinline__ float q8_scale(const T* scales, int64_t idx) {
+  if constexpr (KIND == 2) return reinterpret_cast<const float*>(scales)[idx];
+  else return Elem<T>::load(scales + idx);
+}
+
 template <typename T, int KIND>
 __device__ __forceinline__ uint32_t q8_code(float x, float s) {
-  return q8_code_of<T, KIND>(round_to<T>(__fdiv_rn(x, s)));
+  const float v = __fdiv_rn(x, s);
+  return q8_code_of<T, KIND>(KIND == 2 ? v : round_to<T>(v));
 }
 
 // vec: a thread owns one 32-byte vector of x (E elements that share a scale): the IEEE quotients come from the
@@ -359,7 +369,7 @@ __global__ void __launch_bounds__(kThreads) pack8_kernel(const T* __restrict__ x
     const V32* xv = reinterpret_cast<const V32*>(x);
     for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < nv; i += (int64_t)gridDim.x * kThreads) {
       const V32 v = ld_stream(xv + i);
-      const float s = Elem<T>::load(scales + map.index(i * E));
+      const float s = q8_scale<T, KIND>(scales, map.index(i * E));
       float f[E];
       Elem<T>::unpack(v, f);
       const DivSeq2 dv(s);
@@ -383,7 +393,7 @@ __global__ void __launch_bounds__(kThreads) pack8_kernel(const T* __restrict__ x
           a = __fdiv_rn(a, s);
           b = __fdiv_rn(b, s);
         }
-        round_to2<T>(a, b);
+        if constexpr (KIND != 2) round_to2<T>(a, b);
         uint32_t pair;
         if constexpr (KIND == 0) {  // round-to-nearest-even, saturating, NaN -> 0: one conversion each
           int c0, c1;
@@ -414,7 +424,7 @@ __global__ void __launch_bounds__(kThreads) pack8_kernel(const T* __restrict__ x
     }
   } else {
     for (int64_t i = (int64_t)blockIdx.x * kThreads + threadIdx.x; i < n; i += (int64_t)gridDim.x * kThreads)
-      q[i] = (uint8_t)q8_code<T, KIND>(Elem<T>::load(x + i), Elem<T>::load(scales + map.index(i)));
+      q[i] = (uint8_t)q8_code<T, KIND>(Elem<T>::load(x + i), q8_scale<T, KIND>(scales, map.index(i)));
   }
 }
 
@@ -604,7 +614,7 @@ extern "C" int mo_q8_pack(const void* x, uint8_t* q, const void* scales, const i
   const int64_t n = dims[0] * dims[1] * dims[2];
   if (n == 0) return MO_OK;
   if (!x || !q || !scales) { set_error("mo_q8_pack: NULL pointer"); return MO_ERR_NULL; }
-  if (!map_ok(dims + 1) || dims[0] < 0 || (kind != 0 && kind != 1)) { set_error("mo_q8_pack: bad dims / kind"); return MO_ERR_ARG; }
+  if (!map_ok(dims + 1) || dims[0] < 0 || kind < 0 || kind > 2) { set_error("mo_q8_pack: bad dims / kind"); return MO_ERR_ARG; }
   const ScaleMap map = make_map(dims, n);
   const int ev = dtype == MO_F32 ? 8 : 16;
   const int vec = dims[2] % ev == 0 && dims[5] % ev == 0 && aligned32(x) && (reinterpret_cast<uintptr_t>(q) & 15u) == 0;
@@ -612,9 +622,9 @@ extern "C" int mo_q8_pack(const void* x, uint8_t* q, const void* scales, const i
   const int64_t work = vec ? n / ev : n;
 #define MO_Q8(T, K) pack8_kernel<T, K><<<resident_grid((const void*)pack8_kernel<T, K>, (work + kThreads - 1) / kThreads), kThreads, 0, s>>>(static_cast<const T*>(x), q, static_cast<const T*>(scales), n, map, vec)
   switch (dtype) {
-    case MO_F32: if (kind == 0) MO_Q8(float, 0); else MO_Q8(float, 1); break;
-    case MO_F16: if (kind == 0) MO_Q8(__half, 0); else MO_Q8(__half, 1); break;
-    case MO_BF16: if (kind == 0) MO_Q8(__nv_bfloat16, 0); else MO_Q8(__nv_bfloat16, 1); break;
+    case MO_F32: if (kind == 0) MO_Q8(float, 0); else if (kind == 1) MO_Q8(float, 1); else MO_Q8(float, 2); break;
+    case MO_F16: if (kind == 0) MO_Q8(__half, 0); else if (kind == 1) MO_Q8(__half, 1); else MO_Q8(__half, 2); break;
+    case MO_BF16: if (kind == 0) MO_Q8(__nv_bfloat16, 0); else if (kind == 1) MO_Q8(__nv_bfloat16, 1); else MO_Q8(__nv_bfloat16, 2); break;
     default: set_error("mo_q8_pack: unsupported dtype %d", dtype); return MO_ERR_DTYPE;
   }
 #undef MO_Q8

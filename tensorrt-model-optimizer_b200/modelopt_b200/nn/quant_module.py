@@ -270,6 +270,34 @@ class _QuantLinear(QuantLinearConvBase):
             out = torch.nn.functional.linear(x, w, self.bias)
         return self.output_quantizer(out)
 
+    # ---- opt-in: FP8 per-tensor W8A8 on tcgen05 kind::f8f6f4 (backends/fp8_per_tensor_gemm.py) ----
+    @staticmethod
+    def _is_fp8_per_tensor_calibrated(q):
+        return (isinstance(q, TensorQuantizer) and not q._disabled and q._if_quant and not q._if_calib and q.is_fp8
+                and q.backend is None and hasattr(q, "_amax") and q._amax.numel() == 1 and q.pre_quant_scale is None)
+
+    def _real_fp8_ok(self, input):
+        w = self._parameters["weight"]
+        return (self.real_quant_gemm and self._is_fp8_per_tensor_calibrated(self.input_quantizer)
+                and self._is_fp8_per_tensor_calibrated(self.weight_quantizer) and not self.output_quantizer.is_enabled
+                and w.shape[1] % 16 == 0 and w.shape[0] % 8 == 0 and input.dtype in (torch.bfloat16, torch.float16))
+
+    def packed_fp8_weight(self):
+        """(E4M3 codes, scale_b) of the weight (`_to_fp8(weight, amax / 448)`), cached like ``quantized_weight``."""
+        from .. import ops
+
+        w = self._parameters["weight"]
+        q = self.weight_quantizer
+        key = (w.data_ptr(), w._version, tuple(w.shape), w.dtype, q.cache_key())
+        hit = self.__dict__.get("_w8_cache")
+        if hit is not None and hit[0] == key:
+            return hit[1]
+        with torch.no_grad():
+            scale_b = ops.div_scalar(q._amax.float().reshape(1), 448.0)
+            packed = (ops.q8_pack(w.detach(), scale_b, "fp8_sat"), scale_b)
+        self.__dict__["_w8_cache"] = (key, packed)
+        return packed
+
     def forward(self, input, *args, **kwargs):
         if hasattr(self._parameters.get("weight"), "get_qtensor") and not args and not kwargs \
                 and type(self)._original_cls.forward is nn.Linear.forward:
@@ -277,6 +305,12 @@ class _QuantLinear(QuantLinearConvBase):
         if self._tcgen05_ok(input, args, kwargs):
             from .. import ops
 
+            if self._real_fp8_ok(input):
+                scale_a = ops.div_scalar(self.input_quantizer._amax.float().reshape(1), 448.0)
+                a = ops.q8_pack(input.reshape(-1, input.shape[-1]), scale_a, "fp8_sat")
+                wq, scale_b = self.packed_fp8_weight()
+                out = ops.linear_fp8(a, wq, scale_a, scale_b, self.bias, out_dtype=input.dtype)
+                return out.reshape(*input.shape[:-1], out.shape[-1])
             if self._real_nvfp4_ok(input):
                 a = ops.nvfp4_quantize_operand(input.reshape(-1, input.shape[-1]),
                                                self.input_quantizer._amax.float().amax(), 128)

@@ -670,7 +670,8 @@ def q8_pack(x, scales, kind):
     (per-tensor, per-axis keepdims, or N-D blocks [.., n_i / block_i, ..])."""
     _cuda(x, "q8_pack")
     x = x.contiguous()
-    scales = scales.to(device=x.device, dtype=x.dtype).contiguous()
+    # 'fp8_sat' (`_to_fp8`, compiled: fp32 quotient of an fp32 scale, clamped): the scale stays fp32
+    scales = scales.to(device=x.device, dtype=torch.float32 if kind == "fp8_sat" else x.dtype).contiguous()
     ss = list(scales.shape)
     if scales.numel() == 1:
         ss = [1] * x.dim()
@@ -680,8 +681,29 @@ def q8_pack(x, scales, kind):
     q = torch.empty(x.shape, dtype=torch.int8 if kind == "int8" else torch.float8_e4m3fn, device=x.device)
     with _dev(x):
         _launched(_lib.load().mo_q8_pack(x.data_ptr(), q.data_ptr(), scales.data_ptr(), dims, _code(x),
-                                         0 if kind == "int8" else 1, _stream(x)), "mo_q8_pack")
+                                         {"int8": 0, "fp8": 1, "fp8_sat": 2}[kind], _stream(x)), "mo_q8_pack")
     return q
+
+
+def linear_fp8(a, b, scale_a, scale_b, bias=None, out_dtype=torch.bfloat16, out=None):
+    """(a [.., K] e4m3) @ (b [N, K] e4m3)^T * scale_a * scale_b (+ bias) on tcgen05 kind::f8f6f4 (``torch._scaled_mm``
+    with per-tensor scales, backends/fp8_per_tensor_gemm.py:36-50)."""
+    _cuda(a, "linear_fp8")
+    assert a.dtype == torch.float8_e4m3fn and b.dtype == torch.float8_e4m3fn and b.dim() == 2
+    K = a.shape[-1]
+    a2 = a.reshape(-1, K).contiguous()
+    b = b.contiguous()
+    M, N = a2.shape[0], b.shape[0]
+    assert b.shape[1] == K
+    y = torch.empty((M, N), dtype=out_dtype, device=a.device) if out is None else out
+    sa, sb = _f32_vec(scale_a, a2), _f32_vec(scale_b, a2)
+    if bias is not None:
+        bias = bias.to(device=a.device, dtype=out_dtype).contiguous()
+    with _dev(a2):
+        _launched(_lib.load().mo_linear_fp8(a2.data_ptr(), b.data_ptr(), sa.data_ptr(), sb.data_ptr(),
+                                            None if bias is None else bias.data_ptr(), y.data_ptr(), M, N, K, _code(y),
+                                            _stream(a2)), "mo_linear_fp8")
+    return y.reshape(*a.shape[:-1], N)
 
 
 def q8_unpack(q, scales, dtype, kind):
