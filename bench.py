@@ -200,22 +200,21 @@ class HostWorkload:
         self.w = [pinned((co, ci)) for _, co, ci in LINEARS]  # one layer's weights, re-sent for every layer
         self.wy = [pinned((co, ci), False) for _, co, ci in LINEARS]
         per_layer = sum(t.numel() for t in self.x) + sum(t.numel() for t in self.w)
-        # collect reads every tensor once (H2D), fake-quant reads it again (H2D) and returns it (D2H)
-        self.h2d = 2 * 2 * per_layer * a.layers
+        # one pipelined call per layer (mo_calib_qdq_host_batch): every tensor is uploaded ONCE (it stays resident on the
+        # device between its amax and its fake-quant) and returned once
+        self.h2d = 2 * per_layer * a.layers
         self.d2h = 2 * per_layer * a.layers
+        self.running = [0.0] * (2 * len(LINEARS) * a.layers)  # MaxCalibrator state per quantizer
         self.last = None
 
     def step(self):
         ops = self.ops
-        nv = self.a.workload == "nvfp4"
-        for _ in range(self.a.layers):
-            for i in range(len(LINEARS)):
-                for src, dst in ((self.x[i], self.y[i]), (self.w[i], self.wy[i])):
-                    am = ops.amax_host(src)
-                    if nv:
-                        ops.qdq_nvfp4_dynamic_host(src, am, 16, None, out=dst)
-                    else:
-                        ops.qdq_fp8_host(src, am, out=dst)
+        kind = "nvfp4" if self.a.workload == "nvfp4" else "fp8"
+        srcs = [t for i in range(len(LINEARS)) for t in (self.x[i], self.w[i])]
+        dsts = [t for i in range(len(LINEARS)) for t in (self.y[i], self.wy[i])]
+        # collect (running max) + fake-quant of every layer's 14 tensors in ONE pipelined call: the upload of tensor i+1
+        # overlaps the fake-quant and download of tensor i, with no bubble between layers
+        ops.calib_qdq_host_batch(srcs * self.a.layers, self.running, kind, 16, None, outs=dsts * self.a.layers)
         self.last = float(self.wy[-1].view(-1)[0])  # the D2H result is read on the host
 
 
@@ -383,8 +382,8 @@ def main():
             dist.all_reduce(dt, op=dist.ReduceOp.MAX)
         e2e = {"value": a.tokens * world / float(dt.item()), "unit": UNIT, "h2d_bytes_per_step": hw.h2d,
                "d2h_bytes_per_step": hw.d2h, "ms_per_step": float(dt.item()) * 1e3, "steps": a.e2e_steps,
-               "api": "mo_amax_host + mo_qdq_nvfp4_dynamic_host (include/modelopt_b200.h) on pinned host tensors"
-               if a.workload == "nvfp4" else "mo_amax_host + mo_qdq_fp8_host on pinned host tensors"}
+               "api": "mo_calib_qdq_host_batch (include/modelopt_b200.h): collect + fake-quant of the step's 448 pinned host "
+                      "tensors in one pipelined call, one upload and one download per tensor"}
         del hw
 
     cpu = None

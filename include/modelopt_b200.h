@@ -402,6 +402,13 @@ int mo_qdq_nvfp4_dynamic_host(const void* x, void* y, int64_t rows, int64_t cols
                               float global_amax, int block, int div_mode);
 /* amax of a host tensor (per-tensor); *amax_out receives the fp32 value. */
 int mo_amax_host(const void* x, int64_t n, int dtype, float* amax_out);
+/* Collect + fake-quant of a BATCH of host tensors (a TensorQuantizer that is calibrating and quantizing in the same
+ * forward, tensor_quantizer.py:1181-1200; equal to mo_amax_host then mo_qdq_*_host per tensor): running_amax[i] =
+ * max(running_amax[i], amax(x_i)), y_i = fake-quant(x_i) under it.  kind 0 = NVFP4 dynamic (`block`), 1 = FP8 per tensor.
+ * Each tensor crosses the bus once per direction (it stays resident on the device between its amax and its fake-quant) and
+ * the upload of tensor i+1 overlaps the fake-quant + download of tensor i.  Host pointers should be pinned. */
+int mo_calib_qdq_host_batch(int n_tensors, const void* const* xs, void* const* ys, const int64_t* rows, const int64_t* cols,
+                            int dtype, float* running_amax, int kind, int block, int numerics);
 
 #ifdef __cplusplus
 }

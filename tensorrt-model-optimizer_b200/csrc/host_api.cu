@@ -171,3 +171,109 @@ extern "C" int mo_amax_host(const void* x, int64_t n, int dtype, float* amax_out
   if (e != cudaSuccess) { set_error("mo_amax_host: %s", cudaGetErrorString(e)); return (int)e; }
   return MO_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Batched "collect + fake-quant" of HOST tensors: for each tensor i, running_amax[i] = max(running_amax[i], amax(x_i)) and
+// y_i = NVFP4 / FP8 fake-quant of x_i under that amax - what TensorQuantizer.forward does for a quantizer that is
+// collecting and quantizing in the same pass (tensor_quantizer.py:1181-1200), and what mo_amax_host followed by
+// mo_qdq_*_host computes, but every tensor crosses the bus ONCE in each direction: the tensor is kept resident on the
+// device between its amax and its fake-quant (two ping-pong buffers), the upload of tensor i+1 runs on one stream while
+// the fake-quant and download of tensor i run on another, so both copy engines stay busy.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace mo {
+
+struct BatchPipe {
+  cudaStream_t s_in = nullptr, s_out = nullptr;
+  cudaEvent_t ready[2], freed[2];
+  void* res[2] = {nullptr, nullptr};   // resident inputs
+  void* outb[2] = {nullptr, nullptr};  // fake-quantized outputs awaiting download
+  size_t cap = 0;
+  uint32_t* d_bits = nullptr;  // per-tensor amax bit patterns
+  float* d_amax = nullptr;     // per-tensor running amax (in: uploaded, out: merged)
+  int n_cap = 0;
+  int ensure(size_t bytes, int n) {
+    cudaError_t e = cudaSuccess;
+    if (!s_in) {
+      e = cudaStreamCreateWithFlags(&s_in, cudaStreamNonBlocking);
+      if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&s_out, cudaStreamNonBlocking);
+      for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+        e = cudaEventCreateWithFlags(&ready[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&freed[i], cudaEventDisableTiming);
+      }
+    }
+    if (e == cudaSuccess && bytes > cap) {
+      for (int i = 0; i < 2; ++i) { cudaFree(res[i]); cudaFree(outb[i]); res[i] = outb[i] = nullptr; }
+      for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+        e = cudaMalloc(&res[i], bytes);
+        if (e == cudaSuccess) e = cudaMalloc(&outb[i], bytes);
+      }
+      cap = e == cudaSuccess ? bytes : 0;
+    }
+    if (e == cudaSuccess && n > n_cap) {
+      cudaFree(d_bits); cudaFree(d_amax);
+      e = cudaMalloc(&d_bits, (size_t)n * 4);
+      if (e == cudaSuccess) e = cudaMalloc(&d_amax, (size_t)n * 4);
+      n_cap = e == cudaSuccess ? n : 0;
+    }
+    if (e != cudaSuccess) { set_error("batch host pipeline: %s", cudaGetErrorString(e)); return (int)e; }
+    return MO_OK;
+  }
+};
+static BatchPipe g_batch;
+
+// running = max(running, this tensor's amax); amax bit patterns of non-negative floats order like the floats
+__global__ void merge_running_amax_kernel(const uint32_t* bits, float* running) {
+  const uint32_t r = __float_as_uint(*running);
+  *running = __uint_as_float(max(r, *bits));
+}
+
+}  // namespace mo
+
+// kind: 0 = NVFP4 dynamic (block = 16 / 32 / 64), 1 = FP8 E4M3 per tensor
+extern "C" int mo_calib_qdq_host_batch(int n_tensors, const void* const* xs, void* const* ys, const int64_t* rows,
+                                       const int64_t* cols, int dtype, float* running_amax, int kind, int block,
+                                       int numerics) {
+  if (n_tensors == 0) return MO_OK;
+  const int es = esize(dtype);
+  if (!es) { set_error("mo_calib_qdq_host_batch: unsupported dtype %d", dtype); return MO_ERR_DTYPE; }
+  if (!xs || !ys || !rows || !cols || !running_amax || n_tensors < 0) { set_error("mo_calib_qdq_host_batch: NULL pointer"); return MO_ERR_NULL; }
+  if (kind != 0 && kind != 1) { set_error("mo_calib_qdq_host_batch: kind must be 0 (nvfp4) or 1 (fp8)"); return MO_ERR_ARG; }
+  size_t max_bytes = 0;
+  for (int i = 0; i < n_tensors; ++i) {
+    if (rows[i] < 0 || cols[i] < 0 || (rows[i] * cols[i] > 0 && (!xs[i] || !ys[i]))) { set_error("mo_calib_qdq_host_batch: bad tensor %d", i); return MO_ERR_ARG; }
+    const size_t b = (size_t)rows[i] * (size_t)cols[i] * es;
+    if (b > max_bytes) max_bytes = b;
+  }
+  std::lock_guard<std::mutex> lock(g_pipe.mu);
+  BatchPipe& P = g_batch;
+  int rc = P.ensure(max_bytes ? max_bytes : 32, n_tensors);
+  if (rc) return rc;
+  cudaMemcpyAsync(P.d_amax, running_amax, (size_t)n_tensors * 4, cudaMemcpyHostToDevice, P.s_in);
+  cudaMemsetAsync(P.d_bits, 0, (size_t)n_tensors * 4, P.s_in);
+  for (int i = 0; i < n_tensors && rc == MO_OK; ++i) {
+    const int b = i & 1;
+    const int64_t n = rows[i] * cols[i];
+    if (n == 0) continue;
+    // ---- upload + amax on s_in -------------------------------------------------------------------------------
+    if (i >= 2) cudaStreamWaitEvent(P.s_in, P.freed[b], 0);  // the fake-quant of tensor i-2 has read res[b]
+    cudaMemcpyAsync(P.res[b], xs[i], (size_t)n * es, cudaMemcpyHostToDevice, P.s_in);
+    rc = mo_amax(P.res[b], 1, 1, n, dtype, P.d_bits + i, P.s_in);
+    if (rc) break;
+    merge_running_amax_kernel<<<1, 1, 0, P.s_in>>>(P.d_bits + i, P.d_amax + i);
+    cudaEventRecord(P.ready[b], P.s_in);
+    // ---- fake-quant + download on s_out (stream order also protects outb[b] from tensor i-2's download) ------
+    cudaStreamWaitEvent(P.s_out, P.ready[b], 0);
+    if (kind == 0) rc = mo_qdq_nvfp4_dynamic(P.res[b], P.outb[b], rows[i], cols[i], dtype, P.d_amax + i, block, numerics, P.s_out);
+    else rc = mo_qdq_fp8(P.res[b], P.outb[b], n, dtype, P.d_amax + i, 1, n, numerics, P.s_out);
+    if (rc) break;
+    cudaEventRecord(P.freed[b], P.s_out);
+    cudaMemcpyAsync(ys[i], P.outb[b], (size_t)n * es, cudaMemcpyDeviceToHost, P.s_out);
+  }
+  cudaStreamSynchronize(P.s_in);
+  cudaStreamSynchronize(P.s_out);
+  if (rc) return rc;
+  cudaError_t e = cudaMemcpy(running_amax, P.d_amax, (size_t)n_tensors * 4, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  if (e != cudaSuccess) { set_error("mo_calib_qdq_host_batch: %s", cudaGetErrorString(e)); return (int)e; }
+  return MO_OK;
+}

@@ -78,6 +78,8 @@ SIGNATURES = {
     "mo_qdq_int_host": [_p, _p, _i64, _i, _f, _i, _i, _i],
     "mo_qdq_nvfp4_dynamic_host": [_p, _p, _i64, _i64, _i, _f, _i, _i],
     "mo_amax_host": [_p, _i64, _i, C.POINTER(_f)],
+    "mo_calib_qdq_host_batch": [_i, C.POINTER(_p), C.POINTER(_p), C.POINTER(_i64), C.POINTER(_i64), _i, C.POINTER(_f), _i,
+                                _i, _i],
 }
 
 _lib = None

@@ -367,6 +367,30 @@ def amax_host(x: torch.Tensor) -> float:
     return out.value
 
 
+def calib_qdq_host_batch(xs, running_amax, kind="nvfp4", block=16, numerics=None, outs=None):
+    """Collect + fake-quant of a batch of host tensors in one pipelined call: running_amax[i] (list of floats, updated in
+    place) = max(running_amax[i], max|x_i|) and y_i = fake-quant(x_i) under it.  Every tensor crosses the bus once per
+    direction; the upload of x_{i+1} overlaps the fake-quant + download of y_i.  Returns the list of outputs."""
+    n = len(xs)
+    assert len(running_amax) == n
+    for t in xs:
+        _host(t, "calib_qdq_host_batch")
+    ys = [torch.empty_like(t) for t in xs] if outs is None else outs
+    code = _code(xs[0])
+    assert all(_code(t) == code for t in xs), "one dtype per batch"
+    xp = (C.c_void_p * n)(*[t.data_ptr() for t in xs])
+    yp = (C.c_void_p * n)(*[t.data_ptr() for t in ys])
+    cols = [t.shape[-1] if t.dim() else 1 for t in xs]
+    rows = (C.c_int64 * n)(*[t.numel() // max(c, 1) for t, c in zip(xs, cols)])
+    colsa = (C.c_int64 * n)(*cols)
+    am = (C.c_float * n)(*[float(a) for a in running_amax])
+    _launched(_lib.load().mo_calib_qdq_host_batch(n, xp, yp, rows, colsa, code, am, 0 if kind == "nvfp4" else 1, int(block),
+                                                  _mode(numerics)), "mo_calib_qdq_host_batch", n=3 * n)
+    for i in range(n):
+        running_amax[i] = am[i]
+    return ys
+
+
 def qdq_fp8_host(x: torch.Tensor, amax: float, out: torch.Tensor | None = None, numerics=None) -> torch.Tensor:
     _host(x, "qdq_fp8_host")
     y = torch.empty_like(x) if out is None else out

@@ -366,3 +366,33 @@ def test_reference_cuda_ext_fp8_int8_bit_exact(ops, dn):
     assert _same_bits(ops.qdq_int(gpu(x), gpu(am), 8, False, False).cpu(), from_np(g[f"int8_y_{dn}"], dt)) == 0
     amc = torch.from_numpy(g[f"int8c_amax_{dn}"]).to(dt)
     assert _same_bits(ops.qdq_int(gpu(x), gpu(amc), 8, False, False).cpu(), from_np(g[f"int8c_y_{dn}"], dt)) == 0
+
+
+@pytest.mark.parametrize("kind", ["nvfp4", "fp8"])
+def test_calib_qdq_host_batch_equals_separate_calls(kind):
+    """mo_calib_qdq_host_batch == mo_amax_host followed by mo_qdq_*_host per tensor, with a running amax carried in."""
+    from modelopt_b200 import ops
+
+    torch.manual_seed(4)
+    shapes = [(300, 256), (1, 64), (1024, 4096), (77, 1024), (0, 64), (513, 128)]
+    xs = [(torch.randn(s) * (i + 1)).to(torch.bfloat16).pin_memory() for i, s in enumerate(shapes)]
+    running = [0.0, 100.0, 0.5, 0.0, 3.0, 1e-3]
+    want_am, want = [], []
+    for x, r in zip(xs, running):
+        am = max(r, ops.amax_host(x)) if x.numel() else r
+        want_am.append(am)
+        if not x.numel():
+            want.append(torch.empty_like(x))
+        elif kind == "nvfp4":
+            want.append(ops.qdq_nvfp4_dynamic_host(x, am, 16))
+        else:
+            want.append(ops.qdq_fp8_host(x, am))
+    got_am = list(running)
+    got = ops.calib_qdq_host_batch(xs, got_am, kind)
+    assert got_am == pytest.approx(want_am, rel=0, abs=0)
+    for a, b in zip(got, want):
+        assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+    # second pass: the running amax only grows
+    again = list(got_am)
+    ops.calib_qdq_host_batch(xs, again, kind)
+    assert again == got_am
