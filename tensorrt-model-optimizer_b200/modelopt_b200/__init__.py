@@ -18,6 +18,7 @@ from .config import *  # noqa: F401,F403
 from .conversion import *  # noqa: F401,F403
 from .model_calib import *  # noqa: F401,F403
 from .model_quant import *  # noqa: F401,F403
+from .backends import *  # noqa: F401,F403
 from .compress import *  # noqa: F401,F403
 from . import gptq  # noqa: F401  (module: gptq.gptq(model, forward_loop, ...) / algorithm "gptq")
 from .nn import (QuantModuleRegistry, TensorQuantizer, is_registered_quant_backend, register_quant_backend,  # noqa: F401

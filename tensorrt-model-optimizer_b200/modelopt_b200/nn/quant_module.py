@@ -224,8 +224,22 @@ class _QuantLinear(QuantLinearConvBase):
         self.__dict__["_wq_cache"] = (key, wq)
         return wq
 
-    # ---- opt-in: NVFP4 W4A4 on the block-scaled tensor-core path (real codes, not the bf16 simulation) ----
-    real_quant_gemm = False
+    # ---- opt-in: real-quant GEMMs (FP8 per-tensor, NVFP4 W4A4) on the tensor-core paths, not the bf16 simulation ----
+    # `module.real_quant_gemm = True` or `enable_real_quant_gemm(model)` (backends.py; quant_linear.py:196-244)
+    @property
+    def real_quant_gemm(self):
+        return bool(self.__dict__.get("_use_real_quant_gemm", False))
+
+    @real_quant_gemm.setter
+    def real_quant_gemm(self, value):
+        self.__dict__["_use_real_quant_gemm"] = bool(value)
+        self.__dict__.pop("_real_quant_gemm_impl", None)
+
+    @property
+    def _should_run_real_quant_gemm(self):
+        """quant_linear.py:203-210."""
+        iq = self.input_quantizer
+        return self.real_quant_gemm and not (iq.is_enabled and iq._if_calib)
 
     @staticmethod
     def _is_nvfp4_dynamic_calibrated(q):
@@ -305,17 +319,12 @@ class _QuantLinear(QuantLinearConvBase):
         if self._tcgen05_ok(input, args, kwargs):
             from .. import ops
 
-            if self._real_fp8_ok(input):
-                scale_a = ops.div_scalar(self.input_quantizer._amax.float().reshape(1), 448.0)
-                a = ops.q8_pack(input.reshape(-1, input.shape[-1]), scale_a, "fp8_sat")
-                wq, scale_b = self.packed_fp8_weight()
-                out = ops.linear_fp8(a, wq, scale_a, scale_b, self.bias, out_dtype=input.dtype)
-                return out.reshape(*input.shape[:-1], out.shape[-1])
-            if self._real_nvfp4_ok(input):
-                a = ops.nvfp4_quantize_operand(input.reshape(-1, input.shape[-1]),
-                                               self.input_quantizer._amax.float().amax(), 128)
-                out = ops.linear_nvfp4(*a, *self.packed_nvfp4_weight(), self.bias, out_dtype=input.dtype)
-                return out.reshape(*input.shape[:-1], out.shape[-1])
+            if self._should_run_real_quant_gemm and input.numel() > 1:
+                from ..backends import gemm_registry
+
+                impl = gemm_registry.find_match(self, input)  # quant_linear.py:212-221
+                if impl is not None:
+                    return impl(self, input, self._parameters["weight"], self.bias)
             q = self.input_quantizer
             fmt = self._fused_input_format(q, input)
             if fmt is not None:  # input fake-quant inside the GEMM's operand prologue: ONE kernel for the linear

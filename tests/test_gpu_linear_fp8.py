@@ -79,3 +79,42 @@ def test_module_real_quant_fp8_path():
         before = ops.LAUNCHES[0]
         model(x)
         assert ops.LAUNCHES[0] - before == 4  # cached weight codes
+
+
+def test_gemm_registry_dispatch():
+    """enable_real_quant_gemm + gemm_registry (backends/gemm_registry.py): default FP8 backend, a user backend registered
+    in front of it, and disable."""
+    from modelopt_b200.backends import GEMMRegistry, gemm_registry
+
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(256, 512)).cuda().to(torch.bfloat16)
+    x = torch.randn(64, 256, device="cuda", dtype=torch.bfloat16)
+    mtq.quantize(model, qcfg.FP8_DEFAULT_CFG, lambda m: m(x))
+    with torch.no_grad():
+        fake = model(x)
+        assert not mtq.is_real_quant_gemm_enabled(model)
+        mtq.enable_real_quant_gemm(model)
+        assert mtq.is_real_quant_gemm_enabled(model) and model[0].real_quant_gemm
+        real = model(x)
+        assert (real.float() - fake.float()).norm() / fake.float().norm() < 0.02
+        calls = []
+
+        def user_gemm(module, input, weight, bias):
+            calls.append(1)
+            return torch.nn.functional.linear(input, weight, bias)
+
+        reg = gemm_registry._registry
+        gemm_registry._registry = []
+        try:
+            gemm_registry.register(user_gemm, None)
+            assert user_gemm in gemm_registry
+            model(x)
+            assert calls == [1]
+            gemm_registry.unregister(user_gemm)
+            assert user_gemm not in gemm_registry
+        finally:
+            gemm_registry._registry = reg
+        mtq.disable_real_quant_gemm(model)
+        assert torch.equal(model(x), fake)
+    r = GEMMRegistry()
+    assert r.find_match(model[0], x) is None
