@@ -112,3 +112,40 @@ def test_fp8_mse_reference_error_and_intended_path(calib):
     o = ohist.HistogramCalibrator((4, 3), None, False)
     o._calib_hist, o._calib_bin_edges = c._calib_hist.cpu(), c._calib_bin_edges.cpu()
     assert a == float(o.compute_amax("mse", intended_mse=True))
+
+
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("skip_zeros", [False, True])
+@pytest.mark.parametrize("nbins", [2048, 3001])
+def test_whole_equals_chunked_and_single_bin_extremes(dt, skip_zeros, nbins):
+    """Size-independent property: the same data counted whole and in chunks gives identical exact counts, including
+    ReLU-like data (half zeros), 2^24 elements in ONE bin (fp32 counters would stop being exact there) and every element
+    equal to the range maximum."""
+    from modelopt_b200 import ops
+
+    torch.manual_seed(0)
+    x = torch.randn(3000, 4096, device="cuda") * 2
+    x[x < 0] = 0  # half of the elements are exactly zero
+    x[7, 9] = 11.0
+    x = x.to(dt)
+    rmax = x.float().abs().amax().reshape(1)
+    whole = torch.zeros(nbins, dtype=torch.int64, device="cuda")
+    ops.hist_into(x, rmax, whole, skip_zeros=skip_zeros)
+    parts = torch.zeros(nbins, dtype=torch.int64, device="cuda")
+    flat = x.reshape(-1)
+    step = (1 << 20) - 4096
+    for off in range(0, flat.numel(), step):
+        ops.hist_into(flat[off:off + step], rmax, parts, skip_zeros=skip_zeros)
+    assert torch.equal(whole, parts)
+    expect = flat.numel() - (int((flat == 0).sum()) if skip_zeros else 0)
+    assert int(whole.sum()) == expect
+    # all elements in ONE bin: 2^24 zeros -> bin 0 exactly (16-bit halves must never carry)
+    z = torch.zeros(1 << 24, device="cuda", dtype=dt)
+    c = torch.zeros(nbins, dtype=torch.int64, device="cuda")
+    ops.hist_into(z, torch.ones(1, device="cuda"), c)
+    assert int(c[0]) == 1 << 24 and int(c[1:].sum()) == 0
+    # all elements equal to the range maximum -> last bin
+    o = torch.ones(1 << 21, device="cuda", dtype=dt)
+    c.zero_()
+    ops.hist_into(o, torch.ones(1, device="cuda"), c)
+    assert int(c[-1]) == 1 << 21 and int(c[:-1].sum()) == 0
