@@ -127,9 +127,11 @@ struct Nf4Lut {
   // (a rounded difference can tie only between adjacent entries: spacing >= 0.08, relative rounding <= 2^-8)
   __device__ __forceinline__ uint32_t nearest(float x) const {
     if (x != x) return 0u;  // argmin over NaNs / the CUDA scan both stay at index 0
-    int k = 0;
-#pragma unroll
-    for (int i = 0; i < 15; ++i) k += x > v[16 + i];
+    // k = #{midpoints < x} by a 4-step binary search over the 15 sorted midpoints (was 15 compares)
+    int k = x > v[16 + 7] ? 8 : 0;
+    k += x > v[16 + k + 3] ? 4 : 0;
+    k += x > v[16 + k + 1] ? 2 : 0;
+    k += x > v[16 + k] ? 1 : 0;
     const int lo = max(k - 1, 0), hi = min(k + 1, 15);
     int best = lo;
     float bd = diff(x, lo);
@@ -182,6 +184,8 @@ __global__ void __launch_bounds__(kThreads) pack4_vec_kernel(const T* __restrict
       if constexpr (KIND == 0) s = int4_scale<T>(m);
       else s = m;
       if ((i & (lanes - 1)) == 0) Elem<T>::store(scales + (i >> lanes_log2), s);
+      const DivSeq2 nf_dv(s);
+      const bool nf_fast = KIND == 1 && nf_dv.ok && m == m && s < 3.0e38f;  // finite block, divisor in the exact window
       uint32_t w[E / 8];
 #pragma unroll
       for (int k = 0; k < E / 8; ++k) w[k] = 0;
@@ -190,7 +194,15 @@ __global__ void __launch_bounds__(kThreads) pack4_vec_kernel(const T* __restrict
         uint32_t byte;
         if constexpr (KIND == 0) byte = int4_byte<T, kKernelForm>(f[k], f[k + 1], s);
         else {
-          float a = __fdiv_rn(f[k], s), b = __fdiv_rn(f[k + 1], s);
+          float a = f[k], b = f[k + 1];
+          if (nf_fast) {  // |x| <= s: the quotient is in [-1, 1]; the division's own FMA sequence, reciprocal hoisted
+            nf_dv(a, b);
+            a = copysignf(a, f[k]);
+            b = copysignf(b, f[k + 1]);
+          } else {
+            a = __fdiv_rn(a, s);
+            b = __fdiv_rn(b, s);
+          }
           round_to2<T>(a, b);
           byte = (lut.nearest(a) << 4) | lut.nearest(b);
         }

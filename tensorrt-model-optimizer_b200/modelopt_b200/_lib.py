@@ -72,6 +72,7 @@ SIGNATURES = {
     "mo_nvfp4_fp8_scale_sweep_hessian": [_p, _i64, _i64, _i, _i, _p, _p, _p, _i, _p],
     "mo_gptq_block_nvfp4": [_p, _p, _p, _p, _f, _p, _i64, _i, _i, _i, _i, _i, _p],
     "mo_linear_fp8": [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p],
+    "mo_linear_fp8_pair": [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p],
     "mo_selftest_e2m1": [C.POINTER(C.c_uint64)],
     "mo_selftest_exact_div": [_i, _i, C.c_uint64, C.POINTER(C.c_uint64)],
     "mo_qdq_fp8_host": [_p, _p, _i64, _i, _f, _i],

@@ -709,7 +709,10 @@ def q8_pack(x, scales, kind):
     return q
 
 
-def linear_fp8(a, b, scale_a, scale_b, bias=None, out_dtype=torch.bfloat16, out=None):
+FP8_PAIR = {"enabled": False}  # route linear_fp8 to the cta_group::2 kernel (set after it is validated on the box)
+
+
+def linear_fp8(a, b, scale_a, scale_b, bias=None, out_dtype=torch.bfloat16, out=None, pair=None):
     """(a [.., K] e4m3) @ (b [N, K] e4m3)^T * scale_a * scale_b (+ bias) on tcgen05 kind::f8f6f4 (``torch._scaled_mm``
     with per-tensor scales, backends/fp8_per_tensor_gemm.py:36-50)."""
     _cuda(a, "linear_fp8")
@@ -723,8 +726,9 @@ def linear_fp8(a, b, scale_a, scale_b, bias=None, out_dtype=torch.bfloat16, out=
     sa, sb = _f32_vec(scale_a, a2), _f32_vec(scale_b, a2)
     if bias is not None:
         bias = bias.to(device=a.device, dtype=out_dtype).contiguous()
+    fn = _lib.load().mo_linear_fp8_pair if (FP8_PAIR["enabled"] if pair is None else pair) else _lib.load().mo_linear_fp8
     with _dev(a2):
-        _launched(_lib.load().mo_linear_fp8(a2.data_ptr(), b.data_ptr(), sa.data_ptr(), sb.data_ptr(),
+        _launched(fn(a2.data_ptr(), b.data_ptr(), sa.data_ptr(), sb.data_ptr(),
                                             None if bias is None else bias.data_ptr(), y.data_ptr(), M, N, K, _code(y),
                                             _stream(a2)), "mo_linear_fp8")
     return y.reshape(*a.shape[:-1], N)
