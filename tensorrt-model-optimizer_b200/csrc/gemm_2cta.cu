@@ -1,0 +1,281 @@
+// Quant-aware linear (bf16 / f16 operands) on CTA PAIRS (tcgen05 cta_group::2): the math of csrc/gemm.cu's plain and loss
+// modes with the 256 x 256 tile of a pair of SMs.  Each CTA of the 2-CTA cluster holds its own 128 rows of A and HALF of the
+// B tile, so per K step a CTA fills and reads 32 KB of shared memory instead of 48 KB for its 128 x 256 of output - the
+// shared-memory bandwidth per SM is what bounds the single-CTA kernel - and the ring is 6 stages deep.
+// Protocol: see csrc/gemm_fp8_2cta.cu (same barriers; the leader's `full` barrier collects the bytes of both CTAs, the
+// MMA commit is multicast to both CTAs' `empty` / `tmem_full`, both epilogues arrive on the leader's `tmem_empty`).
+#include <type_traits>
+
+#include "tc_utils.cuh"
+
+namespace mo {
+
+namespace f16p {
+constexpr int BM = 128, BN = 256, BK = 64;    // per CTA: 128 rows of A, 128 of the 256 B rows; BK elements = 128 bytes
+constexpr int BNH = BN / 2;
+constexpr int UMMA_K = 16;
+constexpr int kStages = 6;
+constexpr int kThreadsG = 192;
+constexpr uint32_t kABytes = BM * BK * 2, kBBytes = BNH * BK * 2, kStageBytes = kABytes + kBBytes;
+constexpr int kGroupM = 8;                    // 8 pair-tiles of 256 rows
+constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // clears the CTA-rank bit of a shared::cluster address (leader's copy)
+
+struct Smem {
+  uint8_t a[kStages][kABytes];
+  uint8_t b[kStages][kBBytes];
+  uint64_t full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ uint32_t cluster_rank16() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all16() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_pair16(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar) & kPeerMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                             uint32_t accumulate) {
+  asm volatile(
+      "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_pair16(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+               ::"r"(smem_u32(bar)), "h"((uint16_t)3)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cta16(uint64_t* bar, uint32_t cta) {
+  asm volatile("{\n .reg .b32 ra;\n mapa.shared::cluster.u32 ra, %0, %1;\n mbarrier.arrive.shared::cluster.b64 _, [ra];\n}"
+               ::"r"(smem_u32(bar)), "r"(cta)
+               : "memory");
+}
+__device__ __forceinline__ void tile_coord(int tile, int tiles_m, int tiles_n, int& m_blk, int& n_blk) {
+  const int per_group = kGroupM * tiles_n;
+  const int g = tile / per_group, r = tile - g * per_group;
+  const int gm = min(kGroupM, tiles_m - g * kGroupM);
+  n_blk = r / gm;
+  m_blk = g * kGroupM + (r - n_blk * gm);
+}
+}  // namespace f16p
+
+template <bool kHalf, bool kLoss>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(f16p::kThreadsG, 1)
+linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                   const void* __restrict__ bias_v, void* __restrict__ out_v, const void* __restrict__ ref_v,
+                   double* __restrict__ loss_acc, double loss_scale, int M, int N, int K) {
+  using namespace f16p;
+  using T = typename std::conditional<kHalf, __half, __nv_bfloat16>::type;
+  extern __shared__ uint8_t smem_raw[];
+  Smem& s = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_rank16();
+  const bool leader = rank == 0;
+  const int tiles_m = (M + 2 * BM - 1) / (2 * BM), tiles_n = (N + BN - 1) / BN, num_tiles = tiles_m * tiles_n;
+  const int num_kb = (K + BK - 1) / BK;
+  const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&s.tmem_full[i], 1); mbar_init(&s.tmem_empty[i], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) {  // the same warp of both CTAs allocates the pair's TMEM (same address in both)
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&s.tmem_base)),
+                 "r"(512u)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all16();  // both CTAs' barriers are initialised before any remote arrive / complete_tx
+  tc_fence_after();
+  const uint32_t tmem = s.tmem_base;
+
+  if (warp == 0) {
+    if (lane == 0) {  // ===== TMA producer (both CTAs) =====
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        int m_blk, n_blk;
+        tile_coord(tile, tiles_m, tiles_n, m_blk, n_blk);
+        const int m0 = m_blk * 2 * BM + (int)rank * BM, n0 = n_blk * BN + (int)rank * BNH;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&s.empty[stage], phase ^ 1);
+          if (leader) mbar_expect_tx(&s.full[stage], 2 * kStageBytes);  // bytes of both CTAs land on this barrier
+          tma_load_2d_pair16(s.a[stage], &map_a, &s.full[stage], kb * BK, m0);
+          tma_load_2d_pair16(s.b[stage], &map_b, &s.full[stage], kb * BK, n0);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0 && leader) {  // ===== MMA issuer (leader CTA only) =====
+      // kind::f16 descriptor: D = F32, A / B = BF16 (1) or F16 (0) K-major, N >> 3 at [17,23), M >> 4 at [24,29), M = 256
+      const uint32_t fmt = kHalf ? 0u : 1u;
+      const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
+      int stage = 0, acc = 0;
+      uint32_t phase = 0, acc_phase = 0;
+      for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+        mbar_wait(&s.tmem_empty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem + (uint32_t)(acc * BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&s.full[stage], phase);
+          tc_fence_after();
+          const uint64_t da = umma_desc(smem_u32(s.a[stage])), db = umma_desc(smem_u32(s.b[stage]));
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k)
+            umma_f16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+          umma_commit_pair16(&s.empty[stage]);
+          if (kb == num_kb - 1) umma_commit_pair16(&s.tmem_full[acc]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else {
+    // ===== epilogue (both CTAs): warps 2..5 own TMEM lanes 32*(warp%4) .. +31 of their CTA's accumulator half =====
+    const int quarter = warp & 3;
+    const T* bias = static_cast<const T*>(bias_v);
+    T* out = static_cast<T*>(out_v);
+    const T* ref = static_cast<const T*>(ref_v);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    float loss = 0.f;
+    double dloss = 0.0;
+    for (int tile = pair; tile < num_tiles; tile += num_pairs) {
+      int m_blk, n_blk;
+      tile_coord(tile, tiles_m, tiles_n, m_blk, n_blk);
+      mbar_wait(&s.tmem_full[acc], acc_phase);
+      tc_fence_after();
+      const int row = m_blk * 2 * BM + (int)rank * BM + quarter * 32 + lane;
+      const int n0 = n_blk * BN;
+      const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(taddr + (uint32_t)c0, r);
+        if (row < M) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 8) {
+            const int col = n0 + c0 + j;
+            if (col < N) {
+              float f[8];
+#pragma unroll
+              for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
+              if (bias != nullptr) {
+                const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
+                const T* bp = reinterpret_cast<const T*>(&bv);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = __fadd_rn(f[i], Elem<T>::load(bp + i));
+              }
+              uint4 o;
+              T* op = reinterpret_cast<T*>(&o);
+#pragma unroll
+              for (int i = 0; i < 8; ++i) Elem<T>::store(op + i, f[i]);
+              if constexpr (kLoss) {
+                const uint4 rv = __ldg(reinterpret_cast<const uint4*>(ref + (int64_t)row * N + col));
+                const T* rp = reinterpret_cast<const T*>(&rv);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                  T dt;
+                  Elem<T>::store(&dt, __fsub_rn(Elem<T>::load(op + i), Elem<T>::load(rp + i)));
+                  const float d = Elem<T>::load(&dt);
+                  loss = __fmaf_rn(d, d, loss);
+                }
+              } else {
+                *reinterpret_cast<uint4*>(out + (int64_t)row * N + col) = o;
+              }
+            }
+          }
+        }
+      }
+      if constexpr (kLoss) { dloss += (double)loss; loss = 0.f; }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cta16(&s.tmem_empty[acc], 0);  // the leader's barrier collects both CTAs' 4 warps
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+    if constexpr (kLoss) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dloss += __shfl_xor_sync(0xffffffffu, dloss, o);
+      if (lane == 0 && dloss != 0.0) atomicAdd(loss_acc, dloss * loss_scale);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all16();  // the peer may still be reading / arriving: nobody frees TMEM or exits early
+  if (warp == 1) {
+    __syncwarp();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+  }
+}
+
+static bool make_map16_pair(CUtensorMap* m, const void* base, int64_t rows, int64_t K, int box_rows, bool half) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return false; }
+  const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)f16p::BK, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(m, half ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return false; }
+  return true;
+}
+
+template <bool kHalf, bool kLoss>
+static int linear_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const void* bias, void* out, const void* ref,
+                              double* loss_acc, int M, int N, int K, cudaStream_t s) {
+  auto kern = linear_pair_kernel<kHalf, kLoss>;
+  const int smem = (int)sizeof(f16p::Smem) + 1024;
+  static bool configured = false;
+  if (!configured) {
+    const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) { set_error("mo_linear_pair: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    configured = true;
+  }
+  const int tiles = ((M + 2 * f16p::BM - 1) / (2 * f16p::BM)) * ((N + f16p::BN - 1) / f16p::BN);
+  const int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
+  kern<<<2 * pairs, f16p::kThreadsG, smem, s>>>(ma, mb, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), M, N, K);
+  return check_launch("mo_linear_pair");
+}
+
+}  // namespace mo
+
+using namespace mo;
+
+extern "C" int mo_linear_pair(const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K,
+                              int dtype, const void* ref, double* loss_acc, void* stream) {
+  if (M < 0 || N < 0 || K < 0) { set_error("mo_linear_pair: bad shape"); return MO_ERR_SHAPE; }
+  if (M == 0 || N == 0) return MO_OK;
+  if (dtype != MO_BF16 && dtype != MO_F16) { set_error("mo_linear_pair: bf16 / f16 only (dtype %d)", dtype); return MO_ERR_DTYPE; }
+  const bool loss = ref != nullptr || loss_acc != nullptr;
+  if (!x || !w || (loss ? (!ref || !loss_acc) : !out)) { set_error("mo_linear_pair: NULL pointer"); return MO_ERR_NULL; }
+  if (K < 8 || K % 8 != 0 || N % 8 != 0) { set_error("mo_linear_pair: K and N must be multiples of 8"); return MO_ERR_SHAPE; }
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) { set_error("mo_linear_pair: dimension too large"); return MO_ERR_SHAPE; }
+  auto mis = [](const void* p) { return p && (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
+  if (mis(x) || mis(w) || mis(bias) || mis(out) || mis(ref)) { set_error("mo_linear_pair: pointers must be 16-byte aligned"); return MO_ERR_ARG; }
+  const bool half = dtype == MO_F16;
+  CUtensorMap ma, mb;
+  if (!make_map16_pair(&ma, x, M, K, f16p::BM, half) || !make_map16_pair(&mb, w, N, K, f16p::BNH, half)) return MO_ERR_ARG;
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int m = (int)M, n = (int)N, k = (int)K;
+  if (half) return loss ? linear_pair_launch<true, true>(ma, mb, bias, out, ref, loss_acc, m, n, k, s)
+                        : linear_pair_launch<true, false>(ma, mb, bias, out, ref, loss_acc, m, n, k, s);
+  return loss ? linear_pair_launch<false, true>(ma, mb, bias, out, ref, loss_acc, m, n, k, s)
+              : linear_pair_launch<false, false>(ma, mb, bias, out, ref, loss_acc, m, n, k, s);
+}

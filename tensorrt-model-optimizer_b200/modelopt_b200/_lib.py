@@ -52,6 +52,7 @@ SIGNATURES = {
     "mo_sq_diff_mean": [_p, _p, _i64, _i, _p, _p],
     "mo_awq_clip_loss": [_p, _p, _i64, _i64, _i, _i64, _i64, _i, _p, _i, C.POINTER(_f), _i, _i, _i, _i, _p, _p],
     "mo_linear": [_p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p, _p],
+    "mo_linear_pair": [_p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p, _p],
     "mo_linear_qdq": [_p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p, _i, _i, _i, _i, _p],
     "mo_linear_nvfp4": [_p, _p, _p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p],
     "mo_nvfp4_pack_gemm": [_p, _i64, _i64, _i, _p, _p, _p, _p],

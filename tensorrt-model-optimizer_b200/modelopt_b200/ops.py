@@ -709,7 +709,8 @@ def q8_pack(x, scales, kind):
     return q
 
 
-FP8_PAIR = {"enabled": False}  # route linear_fp8 to the cta_group::2 kernel (set after it is validated on the box)
+# rows from which linear_fp8 runs on CTA pairs (csrc/gemm_fp8_2cta.cu): bit-identical, 1-7 % faster on the timed shapes
+FP8_PAIR = {"min_rows": 512}
 
 
 def linear_fp8(a, b, scale_a, scale_b, bias=None, out_dtype=torch.bfloat16, out=None, pair=None):
@@ -726,7 +727,8 @@ def linear_fp8(a, b, scale_a, scale_b, bias=None, out_dtype=torch.bfloat16, out=
     sa, sb = _f32_vec(scale_a, a2), _f32_vec(scale_b, a2)
     if bias is not None:
         bias = bias.to(device=a.device, dtype=out_dtype).contiguous()
-    fn = _lib.load().mo_linear_fp8_pair if (FP8_PAIR["enabled"] if pair is None else pair) else _lib.load().mo_linear_fp8
+    use_pair = pair if pair is not None else (FP8_PAIR["min_rows"] is not None and M >= FP8_PAIR["min_rows"])
+    fn = _lib.load().mo_linear_fp8_pair if use_pair else _lib.load().mo_linear_fp8
     with _dev(a2):
         _launched(fn(a2.data_ptr(), b.data_ptr(), sa.data_ptr(), sb.data_ptr(),
                                             None if bias is None else bias.data_ptr(), y.data_ptr(), M, N, K, _code(y),
@@ -998,7 +1000,18 @@ def linear_supported(x, weight, bias=None) -> bool:
     return True
 
 
-def linear(x, weight, bias=None, out=None):
+# rows from which linear / linear_loss_into run on CTA pairs (tcgen05 cta_group::2, csrc/gemm_2cta.cu); None = never.
+# Bit-identical to the single-CTA kernel; 1-5 % faster from 2048 rows up (profiles/r01_gemm_pair.txt); below 512 rows a
+# 256-row pair tile would be mostly padding.
+LINEAR_PAIR = {"min_rows": 512}
+
+
+def _pair_fn(M, pair):
+    use = pair if pair is not None else (LINEAR_PAIR["min_rows"] is not None and M >= LINEAR_PAIR["min_rows"])
+    return _lib.load().mo_linear_pair if use else _lib.load().mo_linear
+
+
+def linear(x, weight, bias=None, out=None, pair=None):
     """x[..., K] @ weight[N, K]^T (+ bias) -> [..., N]; fp32 accumulation in TMEM, output in x.dtype."""
     _cuda(x, "linear")
     if not linear_supported(x, weight, bias):
@@ -1012,12 +1025,12 @@ def linear(x, weight, bias=None, out=None):
     y = torch.empty(*x.shape[:-1], N, dtype=x.dtype, device=x.device) if out is None else out
     assert y.is_contiguous() and y.numel() == M * N and y.dtype == x.dtype
     with _dev(x):
-        _launched(_lib.load().mo_linear(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None,
-                                        y.data_ptr(), M, N, K, _code(x2), None, None, _stream(x)), "mo_linear")
+        _launched(_pair_fn(M, pair)(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None,
+                                    y.data_ptr(), M, N, K, _code(x2), None, None, _stream(x)), "mo_linear")
     return y
 
 
-def linear_loss_into(x, weight, bias, ref, acc):
+def linear_loss_into(x, weight, bias, ref, acc, pair=None):
     """acc (float64 device scalar) += mean((linear(x, weight, bias) - ref)^2) without writing the output."""
     _cuda(x, "linear_loss_into")
     if not linear_supported(x, weight, bias):
@@ -1030,8 +1043,8 @@ def linear_loss_into(x, weight, bias, ref, acc):
     N = w.shape[0]
     assert r.numel() == M * N and r.dtype == x.dtype and acc.dtype == torch.float64 and acc.numel() == 1
     with _dev(x):
-        _launched(_lib.load().mo_linear(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None, None,
-                                        M, N, K, _code(x2), r.data_ptr(), acc.data_ptr(), _stream(x)), "mo_linear")
+        _launched(_pair_fn(M, pair)(x2.data_ptr(), w.data_ptr(), b.data_ptr() if b is not None else None, None,
+                                    M, N, K, _code(x2), r.data_ptr(), acc.data_ptr(), _stream(x)), "mo_linear")
     return acc
 
 

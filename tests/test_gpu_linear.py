@@ -158,3 +158,26 @@ def test_quant_linear_small_batch_uses_one_kernel():
         finally:
             ops.FUSED_PROLOGUE.update(old)
     assert torch.equal(y, y2)
+
+
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (300, 264, 144), (1, 8, 8), (1024, 512, 1024), (4096, 4096, 4096)])
+def test_cta_pair_kernel_equals_single_cta(dt, M, N, K):
+    """csrc/gemm_2cta.cu (tcgen05 cta_group::2, 256 x 256 tile per 2-CTA cluster) == csrc/gemm.cu bit for bit, plain and
+    loss modes; ragged M / N / K exercise the TMA zero fill of a CTA whose half tile is partly or wholly out of range."""
+    from modelopt_b200 import ops
+
+    torch.manual_seed(0)
+    x = torch.randn(M, K, device="cuda", dtype=dt)
+    w = (torch.randn(N, K, device="cuda") * 0.05).to(dt)
+    b = (torch.randn(N, device="cuda") * 0.1).to(dt)
+    one, two = ops.linear(x, w, b, pair=False), ops.linear(x, w, b, pair=True)
+    assert torch.equal(one, two)
+    ref = torch.randn(M, N, device="cuda", dtype=dt)
+    l1 = torch.zeros(1, dtype=torch.float64, device="cuda")
+    l2 = torch.zeros(1, dtype=torch.float64, device="cuda")
+    ops.linear_loss_into(x, w, b, ref, l1, pair=False)
+    ops.linear_loss_into(x, w, b, ref, l2, pair=True)
+    assert abs(l1.item() - l2.item()) <= 1e-12 * max(1.0, abs(l1.item()))  # fp64 atomics: order only
+    want = (x.float() @ w.float().t() + b.float())
+    assert (two.float() - want).abs().max() <= 2.0 ** -7 * want.abs().max() + 1e-6

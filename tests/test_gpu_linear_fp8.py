@@ -118,3 +118,12 @@ def test_gemm_registry_dispatch():
         assert torch.equal(model(x), fake)
     r = GEMMRegistry()
     assert r.find_match(model[0], x) is None
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (300, 264, 144), (1, 8, 16), (1024, 512, 1024), (4096, 4096, 4096)])
+def test_cta_pair_kernel_equals_single_cta(M, N, K):
+    """csrc/gemm_fp8_2cta.cu (cta_group::2) == csrc/gemm_fp8.cu bit for bit."""
+    x, w, sa, sb = _operands(M, N, K)
+    a, b = ops.q8_pack(x, sa, "fp8_sat"), ops.q8_pack(w, sb, "fp8_sat")
+    bv = (torch.randn(N, device="cuda") * 0.1).to(torch.bfloat16)
+    assert torch.equal(ops.linear_fp8(a, b, sa, sb, bv, pair=False), ops.linear_fp8(a, b, sa, sb, bv, pair=True))
