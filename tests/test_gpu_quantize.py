@@ -198,3 +198,32 @@ def test_static_nvfp4_weights_promoted_with_shared_global_amax():
         want_w = ofq.nvfp4_static_qdq(wc.reshape(-1, 16), q._amax.cpu().view(-1, 1), q._global_amax.cpu(), True, 448.0,
                                       None).reshape(wc.shape)
         assert torch.equal(got, want_w), n
+
+
+def _all_presets():
+    from modelopt_b200 import config as qcfg
+
+    return sorted(qcfg.choices)
+
+
+@pytest.mark.parametrize("preset", _all_presets())
+def test_every_preset_quantizes_and_runs(preset):
+    """Every preset in config.choices goes through mtq.quantize on a small MLP and produces a finite output close to the
+    unquantized one (catches wiring breakage of any format / algorithm combination)."""
+    import modelopt_b200 as mtq
+    from modelopt_b200 import config as qcfg
+
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.GELU(), torch.nn.Linear(512, 256)).cuda().to(torch.bfloat16)
+    batches = [torch.randn(64, 256, device="cuda", dtype=torch.bfloat16) for _ in range(2)]
+    ref = model(batches[0]).float()
+
+    def loop(m):
+        for b in batches:
+            m(b)
+
+    mtq.quantize(model, getattr(qcfg, preset), loop)
+    out = model(batches[0]).float()
+    assert out.shape == ref.shape and torch.isfinite(out).all()
+    rel = (out - ref).norm() / ref.norm()
+    assert rel < 0.5, (preset, rel.item())
