@@ -321,6 +321,15 @@ def main():
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     if world > 1:
+        # one process per GPU: keep the rank's threads and its pinned host buffers (first touch) on the CPU cores next
+        # to its GPU, so the host-buffer path does not cross sockets
+        try:
+            import pynvml
+
+            pynvml.nvmlInit()
+            pynvml.nvmlDeviceSetCpuAffinity(pynvml.nvmlDeviceGetHandleByIndex(local))
+        except Exception:  # noqa: BLE001  (affinity is an optimisation only)
+            pass
         dist.init_process_group("nccl", device_id=device)
     from modelopt_b200 import ops
 
