@@ -293,11 +293,11 @@ extern "C" int mo_qdq_fp8(const void* x, void* y, int64_t n, int dtype, const fl
   return mo_qdq_fp8_pqs(x, y, n, dtype, amax, axis_size, inner, numerics, nullptr, 1, stream);
 }
 
-template <bool U>
-static int qdq_int_impl(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
-                        int64_t inner, int num_bits, int narrow_range, uint32_t* status, cudaStream_t s,
-                        const float* pre, int64_t cols) {
-  IntOp<U> op;
+template <bool U, bool PT>
+static int qdq_int_impl2(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
+                         int64_t inner, int num_bits, int narrow_range, uint32_t* status, cudaStream_t s,
+                         const float* pre, int64_t cols) {
+  IntOp<U, PT> op;
   const float bound = (float)((1 << (num_bits - 1 + (U ? 1 : 0))) - 1);  // tensor_quant_gpu.cu:38-41
   op.maxb = bound;
   op.minb = -(bound + (narrow_range ? 0.f : 1.f));                       // :69
@@ -305,14 +305,24 @@ static int qdq_int_impl(const void* x, void* y, int64_t n, int dtype, const floa
   int rc;
   switch (dtype) {
     case MO_F32:  if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 8))) return rc;
-                  return launch_stream<float, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<f32>", pre, cols);
+                  return launch_stream<float, IntOp<U, PT>>(x, y, n, op, s, "mo_qdq_int<f32>", pre, cols);
     case MO_F16:  if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 16))) return rc;
-                  return launch_stream<__half, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<f16>", pre, cols);
+                  return launch_stream<__half, IntOp<U, PT>>(x, y, n, op, s, "mo_qdq_int<f16>", pre, cols);
     case MO_BF16: if ((rc = make_axis(op.ax, amax, n, axis_size, inner, 16))) return rc;
-                  return launch_stream<__nv_bfloat16, IntOp<U>>(x, y, n, op, s, "mo_qdq_int<bf16>", pre, cols);
+                  return launch_stream<__nv_bfloat16, IntOp<U, PT>>(x, y, n, op, s, "mo_qdq_int<bf16>", pre, cols);
   }
   set_error("mo_qdq_int: unsupported dtype %d", dtype);
   return MO_ERR_DTYPE;
+}
+
+// per-tensor amax and no pre_quant_scale: the packed-arithmetic instantiation
+template <bool U>
+static int qdq_int_impl(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
+                        int64_t inner, int num_bits, int narrow_range, uint32_t* status, cudaStream_t s,
+                        const float* pre, int64_t cols) {
+  if (axis_size == 1 && pre == nullptr)
+    return qdq_int_impl2<U, true>(x, y, n, dtype, amax, axis_size, inner, num_bits, narrow_range, status, s, pre, cols);
+  return qdq_int_impl2<U, false>(x, y, n, dtype, amax, axis_size, inner, num_bits, narrow_range, status, s, pre, cols);
 }
 
 extern "C" int mo_qdq_int_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,

@@ -106,7 +106,10 @@ __device__ __forceinline__ float min_nan(float a, float b) {
   return r;
 }
 
-template <bool kUnsigned>
+// kPT: per-tensor specialisation (its own kernel instantiation): the vector loop uses packed fp32 arithmetic.  Keeping both
+// forms in one kernel costs 6 registers and an occupancy step (4 -> 3 CTAs per SM) that the per-channel / per-block modes,
+// which also derive a scale per vector, pay 6 % for.
+template <bool kUnsigned, bool kPT = false>
 struct IntOp {
   AxisArgs ax;
   float minb, maxb;
@@ -151,6 +154,28 @@ struct IntOp {
     return zero ? 0.0f : o;
   }
   __device__ __forceinline__ float q1(float x) { return dfast ? q1t<true>(x) : q1t<false>(x); }
+  // q1t<true> on a pair with packed fp32 arithmetic (FMUL2 / FADD2 / FFMA2: one issue slot for two elements); the same
+  // IEEE operations in the same order per element, so the same bits
+  __device__ __forceinline__ void q2fast(float& x0, float& x1) {
+    if (kUnsigned && (x0 < 0.f || x1 < 0.f)) flags |= MO_FLAG_NEGATIVE_IN_UNSIGNED;
+    float v0, v1;
+    asm("{ .reg .b64 a, s, t; mov.b64 a, {%2, %3}; mov.b64 s, {%4, %4}; mul.rn.f32x2 t, a, s; mov.b64 {%0, %1}, t; }"
+        : "=f"(v0), "=f"(v1) : "f"(x0), "f"(x1), "f"(scale));
+    v0 = max_nan(min_nan(v0, maxb), minb);
+    v1 = max_nan(min_nan(v1, maxb), minb);
+    float o0, o1;
+    asm("{ .reg .b64 v, m, nm, r, nb, q, e;\n"
+        "  mov.b64 v, {%2, %3}; mov.b64 m, {%4, %4}; mov.b64 nm, {%5, %5}; mov.b64 r, {%6, %6}; mov.b64 nb, {%7, %7};\n"
+        "  add.rn.f32x2 v, v, m; add.rn.f32x2 v, v, nm;\n"          // rint: (v + 1.5 * 2^23) - 1.5 * 2^23
+        "  mul.rn.f32x2 q, v, r; fma.rn.f32x2 e, nb, q, v; fma.rn.f32x2 q, r, e, q;\n"  // v / scale (ExactDiv)
+        "  mov.b64 {%0, %1}, q; }"
+        : "=f"(o0), "=f"(o1)
+        : "f"(v0), "f"(v1), "f"(12582912.0f), "f"(-12582912.0f), "f"(dr), "f"(-db));
+    o0 = __uint_as_float((__float_as_uint(o0) & 0x7fffffffu) | (__float_as_uint(x0) & 0x80000000u));
+    o1 = __uint_as_float((__float_as_uint(o1) & 0x7fffffffu) | (__float_as_uint(x1) & 0x80000000u));
+    x0 = zero ? 0.0f : o0;
+    x1 = zero ? 0.0f : o1;
+  }
   template <int N>
   __device__ __forceinline__ void vec(float* f, int64_t idx0) { vec<N>(f, idx0, 0.f, false); }
   template <int N>
@@ -162,7 +187,11 @@ struct IntOp {
       return;
     }
     // one branch per vector, not per element: the exact-division window test is uniform over the vector
-    if (dfast) {
+    if (kPT && dfast) {
+      // packed fp32 (measured: per-tensor INT8 87.5 -> 94.6 % of the copy peak)
+#pragma unroll
+      for (int i = 0; i < N; i += 2) q2fast(f[i], f[i + 1]);
+    } else if (dfast) {
 #pragma unroll
       for (int i = 0; i < N; ++i) f[i] = q1t<true>(f[i]);
     } else {
@@ -180,7 +209,7 @@ struct IntOp {
 };
 
 __device__ __forceinline__ void finish_op(Fp8Op&) {}
-template <bool U>
-__device__ __forceinline__ void finish_op(IntOp<U>& op) { op.finish(); }
+template <bool U, bool P>
+__device__ __forceinline__ void finish_op(IntOp<U, P>& op) { op.finish(); }
 
 }  // namespace mo
