@@ -198,20 +198,21 @@ int mo_mse_sweep(const void* x, int64_t outer, int64_t axis_size, int64_t inner,
  * ---------------------------------------------------------------------------------------------- */
 /* INT-N fake quant whose amax is the max|.| of every `block` consecutive elements of the data itself
  * (TensorQuantizer with block_sizes and no calibrated amax: tensor_quantizer.py:736-751 -> reduce_amax on the
- * [n/block, block] view), with an optional per-column multiply in front (pre_quant_scale, :1143; `prescale` fp32
- * [cols] holding values of the tensor dtype, cols % block == 0).  Replaces the `w*s -> reshape -> amax -> QDQ` chain
+ * [n/block, block] view), with an optional per-column multiply in front (pre_quant_scale, :1143; `prescale`:
+ * [cols] values IN THE TENSOR'S DTYPE, cols % block == 0).  Replaces the `w*s -> reshape -> amax -> QDQ` chain
  * AWQ-lite runs 11x per linear per batch (model_calib.py:1537-1551).  amax_out (nullable): fp32 [n_blocks]. */
-int mo_qdq_int_block_dynamic(const void* x, void* y, int64_t n_blocks, int block, int dtype, const float* prescale,
+int mo_qdq_int_block_dynamic(const void* x, void* y, int64_t n_blocks, int block, int dtype, const void* prescale,
                              int64_t cols, int num_bits, int is_unsigned, int narrow_range, float* amax_out,
                              void* stream);
 /* mo_qdq_int / mo_qdq_fp8 with TensorQuantizer's `inputs * pre_quant_scale` (tensor_quantizer.py:1143) folded into
- * the same pass: p = T(x * prescale[i % cols]) is quantized instead of x.  prescale: fp32 [cols] holding values of
- * the tensor dtype, or NULL (then identical to the plain entry points). */
+ * the same pass: p = T(x * prescale[i % cols]) is quantized instead of x.  prescale: [cols] values in the tensor's
+ * dtype (`dtype`; one 32-byte load per vector instead of 64 bytes of fp32), or NULL (identical to the plain entry
+ * points). */
 int mo_qdq_int_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size, int64_t inner,
-                   int num_bits, int is_unsigned, int narrow_range, uint32_t* status, const float* prescale,
+                   int num_bits, int is_unsigned, int narrow_range, uint32_t* status, const void* prescale,
                    int64_t cols, void* stream);
 int mo_qdq_fp8_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size, int64_t inner,
-                   int numerics, const float* prescale, int64_t cols, void* stream);
+                   int numerics, const void* prescale, int64_t cols, void* stream);
 /* y = T(x * scale[col]) over a [rows, cols] matrix (y == x allowed), and in the same pass the amax of y:
  * amax_mode 0 none, 1 per tensor -> amax_bits[0], 2 per row -> amax_bits[row] (bit patterns, merged with max).
  * Replaces the weight fold + max re-calibration of apply_pre_quant_scale_and_smooth / _apply_weight_pre_quant_scale

@@ -21,11 +21,11 @@ constexpr int kUnroll = 2;
 // unaligned case run the scalar path.
 // ------------------------------------------------------------------------------------------------
 template <typename T>
-__device__ __forceinline__ float prescaled(const T* x, int64_t i, const float* pre, int64_t cols) {
+__device__ __forceinline__ float prescaled(const T* x, int64_t i, const T* pre, int64_t cols) {
   float v = Elem<T>::load(x + i);
   if (pre != nullptr) {
     T t;
-    Elem<T>::store(&t, __fmul_rn(v, __ldg(pre + i % cols)));
+    Elem<T>::store(&t, __fmul_rn(v, Elem<T>::load(pre + i % cols)));
     v = Elem<T>::load(&t);
   }
   return v;
@@ -34,8 +34,8 @@ __device__ __forceinline__ float prescaled(const T* x, int64_t i, const float* p
 template <typename T, typename Op, bool kPre>
 __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                               int64_t n, Op op, bool vectorized,
-                                                              const float* __restrict__ pre_arg, int64_t cols) {
-  const float* pre = kPre ? pre_arg : nullptr;  // compile-time NULL: the plain kernels carry no prescale code
+                                                              const T* __restrict__ pre_arg, int64_t cols) {
+  const T* pre = kPre ? pre_arg : nullptr;  // compile-time NULL: the plain kernels carry no prescale code
   constexpr int E = Elem<T>::kPerVec;
   op.init();
   if (vectorized) {
@@ -65,13 +65,11 @@ __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restric
           float f[E];
           Elem<T>::unpack(v[u], f);
           if constexpr (kPre) {  // inputs * pre_quant_scale, a T tensor in the reference (tensor_quantizer.py:1143)
-            const float* ps = pre + (c * E) % cols;
+            // the scale vector travels in the tensor's dtype (its values ARE of that dtype): one 32-byte load per vector
+            float sc[E];
+            Elem<T>::unpack(ld_cached(pre + (c * E) % cols), sc);
 #pragma unroll
-            for (int i = 0; i < E; i += 4) {
-              const float4 s4 = __ldg(reinterpret_cast<const float4*>(ps + i));
-              f[i] = __fmul_rn(f[i], s4.x); f[i + 1] = __fmul_rn(f[i + 1], s4.y);
-              f[i + 2] = __fmul_rn(f[i + 2], s4.z); f[i + 3] = __fmul_rn(f[i + 3], s4.w);
-            }
+            for (int i = 0; i < E; ++i) f[i] = __fmul_rn(f[i], sc[i]);
             Elem<T>::pack(f, v[u]);
             Elem<T>::unpack(v[u], f);
           }
@@ -95,10 +93,10 @@ __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restric
 
 template <typename T, typename Op>
 static int launch_stream(const void* x, void* y, int64_t n, Op op, cudaStream_t stream, const char* what,
-                         const float* pre = nullptr, int64_t cols = 1) {
+                         const void* pre_v = nullptr, int64_t cols = 1) {
   constexpr int E = Elem<T>::kPerVec;
-  const bool vec = aligned32(x) && aligned32(y) && n >= E &&
-                   (pre == nullptr || (cols % E == 0 && (reinterpret_cast<uintptr_t>(pre) & 15u) == 0));
+  const T* pre = static_cast<const T*>(pre_v);
+  const bool vec = aligned32(x) && aligned32(y) && n >= E && (pre == nullptr || (cols % E == 0 && aligned32(pre)));
   int64_t tiles = vec ? (n / E + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll)
                       : (n + kThreads - 1) / kThreads;
   if (pre != nullptr)
@@ -117,7 +115,7 @@ static int launch_stream(const void* x, void* y, int64_t n, Op op, cudaStream_t 
 // ------------------------------------------------------------------------------------------------
 template <typename T, bool kUnsigned>
 __global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_kernel(const T* __restrict__ x, T* __restrict__ y,
-                                                                    int64_t n_vec, int lanes, const float* __restrict__ pre,
+                                                                    int64_t n_vec, int lanes, const T* __restrict__ pre,
                                                                     int64_t cols, IntOp<kUnsigned> op,
                                                                     float* __restrict__ amax_out) {
   constexpr int E = Elem<T>::kPerVec;
@@ -143,13 +141,10 @@ __global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_kernel(const T* __r
       if (live) {
         Elem<T>::unpack(v[u], f);
         if (pre != nullptr) {
-          const float* ps = pre + (c * E) % cols;
+          float sc[E];
+          Elem<T>::unpack(ld_cached(pre + (c * E) % cols), sc);
 #pragma unroll
-          for (int i = 0; i < E; i += 4) {
-            const float4 s4 = __ldg(reinterpret_cast<const float4*>(ps + i));
-            f[i] = __fmul_rn(f[i], s4.x); f[i + 1] = __fmul_rn(f[i + 1], s4.y);
-            f[i + 2] = __fmul_rn(f[i + 2], s4.z); f[i + 3] = __fmul_rn(f[i + 3], s4.w);
-          }
+          for (int i = 0; i < E; ++i) f[i] = __fmul_rn(f[i], sc[i]);
           Elem<T>::pack(f, v[u]);    // the product is a T tensor in the reference
           Elem<T>::unpack(v[u], f);
         }
@@ -179,7 +174,7 @@ __global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_kernel(const T* __r
 template <typename T, bool kUnsigned>
 __global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_generic_kernel(const T* __restrict__ x, T* __restrict__ y,
                                                                             int64_t n_blocks, int block,
-                                                                            const float* __restrict__ pre, int64_t cols,
+                                                                            const T* __restrict__ pre, int64_t cols,
                                                                             IntOp<kUnsigned> op,
                                                                             float* __restrict__ amax_out) {
   op.flags = 0;
@@ -193,7 +188,7 @@ __global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_generic_kernel(cons
       float p = Elem<T>::load(x + e0 + i);
       if (pre != nullptr) {
         T t;
-        Elem<T>::store(&t, __fmul_rn(p, __ldg(pre + (e0 + i) % cols)));
+        Elem<T>::store(&t, __fmul_rn(p, Elem<T>::load(pre + (e0 + i) % cols)));
         p = Elem<T>::load(&t);
       }
       m = max(m, __float_as_uint(p) & 0x7fffffffu);
@@ -205,7 +200,7 @@ __global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_generic_kernel(cons
       float p = Elem<T>::load(x + e0 + i);
       if (pre != nullptr) {
         T t;
-        Elem<T>::store(&t, __fmul_rn(p, __ldg(pre + (e0 + i) % cols)));
+        Elem<T>::store(&t, __fmul_rn(p, Elem<T>::load(pre + (e0 + i) % cols)));
         p = Elem<T>::load(&t);
       }
       Elem<T>::store(y + e0 + i, op.q1(p));
@@ -215,10 +210,11 @@ __global__ void __launch_bounds__(kThreads) qdq_int_blockdyn_generic_kernel(cons
 }
 
 template <typename T, bool U>
-static int blockdyn_launch(const void* x, void* y, int64_t n_blocks, int block, const float* pre, int64_t cols,
+static int blockdyn_launch(const void* x, void* y, int64_t n_blocks, int block, const void* pre_v, int64_t cols,
                            int num_bits, int narrow_range, float* amax_out, cudaStream_t s) {
   constexpr int E = Elem<T>::kPerVec;
   IntOp<U> op;
+  const T* pre = static_cast<const T*>(pre_v);
   const float bound = (float)((1 << (num_bits - 1 + (U ? 1 : 0))) - 1);
   op.maxb = bound;
   op.minb = -(bound + (narrow_range ? 0.f : 1.f));
@@ -227,7 +223,7 @@ static int blockdyn_launch(const void* x, void* y, int64_t n_blocks, int block, 
   op.ax.amax = nullptr; op.ax.axis_size = 1; op.ax.inner = 1; op.ax.small = false;
   const int lanes = block / E;
   const bool vec = aligned32(x) && aligned32(y) && block % E == 0 && lanes >= 1 && lanes <= 32 &&
-                   (lanes & (lanes - 1)) == 0 && (pre == nullptr || (cols % E == 0 && (reinterpret_cast<uintptr_t>(pre) & 15u) == 0));
+                   (lanes & (lanes - 1)) == 0 && (pre == nullptr || (cols % E == 0 && aligned32(pre)));
   if (vec) {
     const int64_t n_vec = n_blocks * lanes;
     const int64_t tiles = (n_vec + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll);
@@ -260,13 +256,13 @@ static int make_axis(AxisArgs& ax, const float* amax, int64_t n, int64_t axis_si
 
 using namespace mo;
 
-static int check_pre(const float* pre, int64_t cols, int64_t n, const char* what) {
+static int check_pre(const void* pre, int64_t cols, int64_t n, const char* what) {
   if (pre && (cols < 1 || n % cols != 0)) { set_error("%s: cols=%lld must divide n=%lld", what, (long long)cols, (long long)n); return MO_ERR_SHAPE; }
   return MO_OK;
 }
 
 extern "C" int mo_qdq_fp8_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
-                              int64_t inner, int numerics, const float* prescale, int64_t cols, void* stream) {
+                              int64_t inner, int numerics, const void* prescale, int64_t cols, void* stream) {
   if (n == 0) return MO_OK;
   if (!x || !y) { set_error("mo_qdq_fp8: x/y is NULL"); return MO_ERR_NULL; }
   if (int rc0 = check_pre(prescale, cols, n, "mo_qdq_fp8_pqs")) return rc0;
@@ -296,7 +292,7 @@ extern "C" int mo_qdq_fp8(const void* x, void* y, int64_t n, int dtype, const fl
 template <bool U, bool PT>
 static int qdq_int_impl2(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
                          int64_t inner, int num_bits, int narrow_range, uint32_t* status, cudaStream_t s,
-                         const float* pre, int64_t cols) {
+                         const void* pre, int64_t cols) {
   IntOp<U, PT> op;
   const float bound = (float)((1 << (num_bits - 1 + (U ? 1 : 0))) - 1);  // tensor_quant_gpu.cu:38-41
   op.maxb = bound;
@@ -315,11 +311,11 @@ static int qdq_int_impl2(const void* x, void* y, int64_t n, int dtype, const flo
   return MO_ERR_DTYPE;
 }
 
-// per-tensor amax and no pre_quant_scale: the packed-arithmetic instantiation
+// per-tensor amax and no pre_quant_scale: the packed-arithmetic instantiation (with a prescale it measured the same)
 template <bool U>
 static int qdq_int_impl(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
                         int64_t inner, int num_bits, int narrow_range, uint32_t* status, cudaStream_t s,
-                        const float* pre, int64_t cols) {
+                        const void* pre, int64_t cols) {
   if (axis_size == 1 && pre == nullptr)
     return qdq_int_impl2<U, true>(x, y, n, dtype, amax, axis_size, inner, num_bits, narrow_range, status, s, pre, cols);
   return qdq_int_impl2<U, false>(x, y, n, dtype, amax, axis_size, inner, num_bits, narrow_range, status, s, pre, cols);
@@ -327,7 +323,7 @@ static int qdq_int_impl(const void* x, void* y, int64_t n, int dtype, const floa
 
 extern "C" int mo_qdq_int_pqs(const void* x, void* y, int64_t n, int dtype, const float* amax, int64_t axis_size,
                               int64_t inner, int num_bits, int is_unsigned, int narrow_range, uint32_t* status,
-                              const float* prescale, int64_t cols, void* stream) {
+                              const void* prescale, int64_t cols, void* stream) {
   if (n == 0) return MO_OK;
   if (int rc0 = check_pre(prescale, cols, n, "mo_qdq_int_pqs")) return rc0;
   if (!x || !y || !amax) { set_error("mo_qdq_int: x/y/amax is NULL"); return MO_ERR_NULL; }
@@ -348,7 +344,7 @@ extern "C" int mo_qdq_int(const void* x, void* y, int64_t n, int dtype, const fl
 }
 
 extern "C" int mo_qdq_int_block_dynamic(const void* x, void* y, int64_t n_blocks, int block, int dtype,
-                                        const float* prescale, int64_t cols, int num_bits, int is_unsigned,
+                                        const void* prescale, int64_t cols, int num_bits, int is_unsigned,
                                         int narrow_range, float* amax_out, void* stream) {
   if (n_blocks == 0) return MO_OK;
   if (!x || !y) { set_error("mo_qdq_int_block_dynamic: x/y is NULL"); return MO_ERR_NULL; }

@@ -136,14 +136,23 @@ def _via_f32(fn, x, *a, **k):
 
 
 # ------------------------------------------------------------------------------------------------
-def _prescale_vec(prescale, x):
-    """pre_quant_scale as the fp32 copy of its x.dtype values, [x.shape[-1]] (None passes through)."""
+def _prescale_t(prescale, x):
+    """pre_quant_scale as a flat contiguous vector in x.dtype on x.device (no copy when it already is one)."""
+    p = prescale.detach()
+    if p.device != x.device or p.dtype != x.dtype:
+        p = p.to(device=x.device, dtype=x.dtype)
+    return p.contiguous().reshape(-1)
+
+
+def _prescale_vec(prescale, x, f32=False):
+    """(pre_quant_scale vector, cols): in x.dtype for the streaming kernels (their ABI takes the tensor's dtype), as the
+    fp32 copy of its x.dtype values with f32=True (the GEMM prologue); None passes through."""
     if prescale is None:
         return None, 1
     cols = prescale.numel()
     if cols == 0 or x.numel() % cols != 0 or (x.shape[-1] % cols != 0 and cols % x.shape[-1] != 0):
         raise ValueError(f"prescale has {cols} elements, which does not tile the rows of a {tuple(x.shape)} tensor")
-    return _f32_vec(prescale.to(x.dtype), x), cols
+    return (_f32_vec(prescale.to(x.dtype), x) if f32 else _prescale_t(prescale, x)), cols
 
 
 def qdq_int(x, amax, num_bits=8, unsigned=False, narrow_range=True, out=None, status=None, prescale=None):
@@ -866,7 +875,7 @@ def qdq_int_block_dynamic(x, block, num_bits=4, unsigned=False, narrow_range=Fal
     if prescale is not None:
         if prescale.numel() != cols:
             raise ValueError(f"prescale has {prescale.numel()} elements, last dim is {cols}")
-        ps = _f32_vec(prescale.to(x.dtype), x)
+        ps = _prescale_t(prescale, x)
     am = torch.empty(nb, dtype=torch.float32, device=x.device) if return_amax else None
     with _dev(x):
         _launched(_lib.load().mo_qdq_int_block_dynamic(x.data_ptr(), y.data_ptr(), nb, block, _code(x),
@@ -1069,7 +1078,7 @@ def linear_qdq(x, weight, bias, x_amax, num_bits=8, narrow_range=False, prescale
     am = _f32_vec(x_amax, x2)
     if am.numel() != 1:
         raise ValueError("linear_qdq: per-tensor input amax only")
-    ps, _ = _prescale_vec(prescale, x2)
+    ps, _ = _prescale_vec(prescale, x2, f32=True)
     fp8 = num_bits == (4, 3)
     y = torch.empty(*x.shape[:-1], N, dtype=x.dtype, device=x.device) if out is None else out
     with _dev(x):
