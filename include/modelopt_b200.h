@@ -21,7 +21,7 @@
 extern "C" {
 #endif
 
-#define MO_ABI_VERSION 3
+#define MO_ABI_VERSION 4
 
 typedef enum { MO_F32 = 0, MO_F16 = 1, MO_BF16 = 2 } mo_dtype;
 

@@ -18,7 +18,7 @@ MO_FLAG_NEGATIVE_IN_UNSIGNED, MO_FLAG_NEGATIVE_AMAX = 1, 2
 # element / scale formats (the reference's `Types` enum order, gemm/tensor_quant_mx.h:39)
 MO_FMT = {"E4M3": 0, "E5M2": 1, "INT8": 2, "E0M3": 3, "E1M2": 4, "E3M0": 5, "E2M1": 6, "E3M2": 7, "E2M3": 8, "E8M0": 9}
 MO_ERR_ALIGN = -5
-ABI_VERSION = 3
+ABI_VERSION = 4
 
 _p, _i, _i64, _f = C.c_void_p, C.c_int, C.c_int64, C.c_float
 
