@@ -10,6 +10,8 @@
 // >= 64 KB per SM is in flight; no shared memory (no reuse); math in fp32 in exactly the reference's
 // operation order (x*scale -> round -> clamp -> q/scale; never x*(1/scale) for INT).
 #include "common.cuh"
+#include <type_traits>
+
 #include "qdq_ops.cuh"
 
 namespace mo {
@@ -91,6 +93,57 @@ __global__ void __launch_bounds__(kThreads) qdq_stream_kernel(const T* __restric
   finish_op(op);
 }
 
+// pre_quant_scale + fake-quant, row-block tiling: a thread owns ONE column vector of the scale (16 values in registers,
+// read once per tile) and walks kPreRows rows of it, two rows in flight.  The streaming kernel above re-read the 16 scale
+// values through L1 for every vector (as many bytes as the data itself for bf16).
+constexpr int kPreRows = 8;
+
+template <typename T, typename Op>
+__global__ void __launch_bounds__(kThreads) qdq_pre_rows_kernel(const T* __restrict__ x, T* __restrict__ y, int64_t rows,
+                                                                int64_t vpr, Op op, const T* __restrict__ pre) {
+  constexpr int E = Elem<T>::kPerVec;
+  op.init();
+  const V32* xv = reinterpret_cast<const V32*>(x);
+  V32* yv = reinterpret_cast<V32*>(y);
+  const int64_t col_tiles = (vpr + kThreads - 1) / kThreads, row_tiles = (rows + kPreRows - 1) / kPreRows;
+  const bool chunk = op.ax.mode == kPerChunk;
+  for (int64_t tile = blockIdx.x; tile < col_tiles * row_tiles; tile += gridDim.x) {
+    const int64_t ct = tile % col_tiles, rt = tile / col_tiles;
+    const int64_t j = ct * kThreads + threadIdx.x;
+    if (j >= vpr) continue;
+    float sc[E];
+    Elem<T>::unpack(ld_cached(pre + j * E), sc);
+    const int64_t r0 = rt * kPreRows, r1 = min(rows, r0 + (int64_t)kPreRows);
+    for (int64_t r = r0; r < r1; r += 2) {
+      V32 v[2];
+      float am[2] = {0.f, 0.f};
+      int64_t c[2] = {r * vpr + j, (r + 1) * vpr + j};
+      const bool ok[2] = {true, r + 1 < r1};
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (ok[u]) {
+          v[u] = ld_stream(xv + c[u]);
+          if (chunk) am[u] = __ldg(op.ax.amax + op.ax.channel(c[u] * E));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (!ok[u]) continue;
+        float f[E];
+        Elem<T>::unpack(v[u], f);
+#pragma unroll
+        for (int i = 0; i < E; ++i) f[i] = __fmul_rn(f[i], sc[i]);
+        Elem<T>::pack(f, v[u]);  // inputs * pre_quant_scale is a T tensor in the reference (tensor_quantizer.py:1143)
+        Elem<T>::unpack(v[u], f);
+        op.template vec<E>(f, c[u] * E, am[u], chunk);
+        Elem<T>::pack(f, v[u]);
+        st_stream(yv + c[u], v[u]);
+      }
+    }
+  }
+  finish_op(op);
+}
+
 template <typename T, typename Op>
 static int launch_stream(const void* x, void* y, int64_t n, Op op, cudaStream_t stream, const char* what,
                          const void* pre_v = nullptr, int64_t cols = 1) {
@@ -99,6 +152,15 @@ static int launch_stream(const void* x, void* y, int64_t n, Op op, cudaStream_t 
   const bool vec = aligned32(x) && aligned32(y) && n >= E && (pre == nullptr || (cols % E == 0 && aligned32(pre)));
   int64_t tiles = vec ? (n / E + (int64_t)kThreads * kUnroll - 1) / ((int64_t)kThreads * kUnroll)
                       : (n + kThreads - 1) / kThreads;
+  // FP8 only: the INT operator's longer per-element chain needs the occupancy the 80-register row-block kernel gives up
+  // (measured: FP8 86.6 -> 93.4 % of the copy peak, INT8 79.8 -> 72.5 %)
+  if (std::is_same<Op, Fp8Op>::value && pre != nullptr && vec && n % cols == 0) {
+    const int64_t rows = n / cols, vpr = cols / E;
+    const int64_t t2 = ((vpr + kThreads - 1) / kThreads) * ((rows + kPreRows - 1) / kPreRows);
+    qdq_pre_rows_kernel<T, Op><<<resident_grid((const void*)qdq_pre_rows_kernel<T, Op>, t2), kThreads, 0, stream>>>(
+        static_cast<const T*>(x), static_cast<T*>(y), rows, vpr, op, pre);
+    return check_launch(what);
+  }
   if (pre != nullptr)
     qdq_stream_kernel<T, Op, true><<<resident_grid((const void*)qdq_stream_kernel<T, Op, true>, tiles), kThreads, 0, stream>>>(static_cast<const T*>(x), static_cast<T*>(y), n, op, vec, pre, cols);
   else
