@@ -157,3 +157,43 @@ def test_int_cast_ste():
     assert x.grad.tolist() == [0.0, 1.0, 1.0, 1.0, 1.0, 0.0, 0.0]
     assert int_cast_ste(torch.tensor([-3.0, 20.0]), 4, True, True).tolist() == [0.0, 15.0]
     assert int_cast_ste(torch.tensor([-9.0]), 4, False, True).tolist() == [-7.0]
+
+
+def test_scale_map_layouts(mtq):
+    """ops._scale_map: where each element's scale lives for per-tensor / per-axis / N-D block layouts (host logic of
+    mo_q8_pack / mo_q8_unpack): dims = {O, A, I, bo, ba, bi, so, sa, si}."""
+    from modelopt_b200 import ops
+
+    assert ops._scale_map([256, 512], [1, 1]) == [1, 1, 256 * 512, 1, 1, 256 * 512, 1, 1, 1]          # per tensor
+    assert ops._scale_map([256, 512], [256, 1]) == [1, 256, 512, 1, 1, 512, 256, 1, 1]                # per row
+    assert ops._scale_map([256, 512], [1, 512]) == [1, 256, 512, 1, 256, 1, 512, 512, 1]              # per column
+    assert ops._scale_map([256, 512], [2, 4]) == [1, 256, 512, 1, 128, 128, 8, 4, 1]                  # 128 x 128 blocks
+    assert ops._scale_map([4, 256, 512], [4, 2, 4]) == [4, 256, 512, 1, 128, 128, 8, 4, 1]            # per-expert blocks
+    with pytest.raises(AssertionError):
+        ops._scale_map([256, 512], [3, 1])                                                            # does not tile
+    with pytest.raises(NotImplementedError):
+        ops._scale_map([4, 6, 8, 10], [2, 6, 2, 10])                                                  # 4 index groups
+
+
+def test_gemm_registry_and_presets(mtq):
+    from modelopt_b200 import config as qcfg
+    from modelopt_b200.backends import GEMMRegistry
+
+    r = GEMMRegistry()
+    f1, f2 = (lambda *a: 1), (lambda *a: 2)
+    r.register(f1, lambda m, x, a, k: x == "one")
+    r.register(f2, None)
+    assert r.find_match(None, "one") is f1 and r.find_match(None, "other") is f2 and f1 in r
+    r.unregister(f2)
+    assert r.find_match(None, "other") is None and f2 not in r
+    for name in ("MXFP8_DEFAULT_CFG", "MXFP6_DEFAULT_CFG", "MXFP4_DEFAULT_CFG", "MXINT8_DEFAULT_CFG", "W4A8_MXFP4_FP8_CFG",
+                 "NVFP4_W4A4_WEIGHT_LOCAL_HESSIAN_CFG", "NVFP4_W4A4_WEIGHT_MSE_FP8_SWEEP_CFG"):
+        cfg = getattr(qcfg, name)
+        assert name in qcfg.choices and isinstance(cfg["quant_cfg"], list)
+    mx = next(e for e in qcfg.MXFP8_DEFAULT_CFG["quant_cfg"] if e.get("quantizer_name") == "*weight_quantizer")["cfg"]
+    assert mx["num_bits"] == (4, 3) and mx["block_sizes"] == {-1: 32, "type": "dynamic", "scale_bits": (8, 0)}
+    assert qcfg.MXFP8_DEFAULT_CFG["algorithm"] is None
+    assert qcfg.NVFP4_W4A4_WEIGHT_LOCAL_HESSIAN_CFG["algorithm"] == {"method": "local_hessian", "fp8_scale_sweep": True}
+    from modelopt_b200.model_quant import _algorithms
+
+    assert {"max", "mse", "local_hessian", "gptq", "smoothquant", "awq_lite", "awq_clip", "awq_full"} <= set(_algorithms())
