@@ -307,6 +307,26 @@ class _LocalHessianAccumulator:
         return local_hessian_error
 
 
+def sync_local_hessians(accumulators, group=None):
+    """all-reduce(SUM) of every accumulator's raw Hessian and sample count over the data-parallel group, in ONE flat
+    buffer (accumulators are visited in creation order, which is the same on every rank of a data-parallel replica)."""
+    accs = [a for a in accumulators if a.is_enabled and a.hessian_per_block is not None]
+    if not accs or not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return
+    dev = accs[0].hessian_per_block.device
+    flat = torch.cat([a.hessian_per_block.reshape(-1).double() for a in accs]
+                     + [torch.tensor([float(a.num_samples) for a in accs], dtype=torch.float64, device=dev)])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    off = 0
+    for a in accs:
+        n = a.hessian_per_block.numel()
+        a.hessian_per_block.copy_(flat[off:off + n].reshape(a.hessian_per_block.shape).float())
+        off += n
+    for i, a in enumerate(accs):
+        a.num_samples = int(round(float(flat[off + i])))
+        a._normalized_hessian = None
+
+
 @torch.no_grad()
 def local_hessian_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, step_size: float = 0.1,
                             start_multiplier: float = 0.25, stop_multiplier: float = 4.0, fp8_scale_sweep: bool = True,
@@ -355,8 +375,13 @@ def local_hessian_calibrate(model: nn.Module, forward_loop=None, distributed_syn
         for sub in disabled:
             sub.enable()
     if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
-        warnings.warn("local_hessian: Hessian is not synced across ranks; refined weight amaxes may diverge under "
-                      "tensor/data parallelism. Treat local_hessian as single-rank for now.")
+        if distributed_sync:
+            # data parallel: every rank saw other batches of the SAME layers, so H = sum X^T X and the sample count add up
+            # (the reference leaves this as a TODO and warns, model_calib.py:1081-1087; with one rank nothing changes)
+            sync_local_hessians(list(accumulators.values()))
+        else:
+            warnings.warn("local_hessian: Hessian is not synced across ranks; refined weight amaxes may diverge under "
+                          "tensor/data parallelism.")
     error_funcs = {qid: acc.build_error_func(keep_buffer=debug) for qid, acc in accumulators.items()}
     hessians = {qid: acc.normalized_hessian() for qid, acc in accumulators.items()}
     _mse_calibrate_weights(model, step_size, start_multiplier, stop_multiplier, fp8_scale_sweep,
@@ -365,7 +390,7 @@ def local_hessian_calibrate(model: nn.Module, forward_loop=None, distributed_syn
         model._local_hessian_accumulators = accumulators
 
 
-__all__ += ["mse_calibrate", "local_hessian_calibrate"]
+__all__ += ["mse_calibrate", "local_hessian_calibrate", "sync_local_hessians"]
 
 
 # =================================================================================================

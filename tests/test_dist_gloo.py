@@ -116,6 +116,30 @@ def _hist_sync(rank, world):
     assert float(cal._calib_bin_edges[-1]) == 1250.0
 
 
-@pytest.mark.parametrize("fn", ["_arena_sync", "_quantize_sync", "_hist_sync"])
+def _hessian_sync(rank, world):
+    """local-Hessian accumulators: after the sync every rank holds the Hessian of ALL ranks' tokens."""
+    from modelopt_b200.model_calib import _LocalHessianAccumulator, sync_local_hessians
+
+    g = torch.Generator().manual_seed(5)
+    xs = [torch.randn(24 + 8 * r, 64, generator=g) for r in range(world)]  # ragged token counts per rank
+    accs = [_LocalHessianAccumulator(32, 64, 16), _LocalHessianAccumulator(32, 64, 32), _LocalHessianAccumulator(8, 60, 16)]
+    for a in accs:
+        a.accumulate(xs[rank][:, :a.cin])
+        a.normalized_hessian()  # cached before the sync on purpose: the sync must drop it
+    sync_local_hessians(accs)
+    allx = torch.cat(xs)
+    for a in accs[:2]:
+        xt = allx.T.reshape(a.num_blocks_per_cin, a.block_size, -1)
+        want = xt @ xt.transpose(-1, -2) / allx.shape[0]
+        assert a.num_samples == allx.shape[0]
+        torch.testing.assert_close(a.normalized_hessian(), want, rtol=1e-5, atol=1e-5)
+    assert not accs[2].is_enabled and accs[2].hessian_per_block is None
+    got = accs[0].normalized_hessian().clone()
+    gathered = [torch.empty_like(got) for _ in range(world)]
+    dist.all_gather(gathered, got)
+    assert all(torch.equal(t, gathered[0]) for t in gathered)  # bit-identical on every rank
+
+
+@pytest.mark.parametrize("fn", ["_arena_sync", "_quantize_sync", "_hist_sync", "_hessian_sync"])
 def test_world_size_2(fn):
     _spawn(fn)
