@@ -103,6 +103,9 @@ __device__ __forceinline__ float round_T(float f) {
   return Elem<T>::load(&t);
 }
 
+// Tried: four rows in flight per warp (loads issued before the arithmetic) — 80-90 registers instead of ~50 cost more
+// occupancy than the extra loads gained (weight_scale 0.234 -> 0.246 ms, |x| column sum 0.098 -> 0.105 ms at
+// [16384, 14336] bf16), so the loop stays one row per warp per iteration.
 template <typename T, bool kWeightScale>
 __global__ void __launch_bounds__(kThreads) col_sum_kernel(const T* __restrict__ x, int64_t rows, int64_t cols,
                                                            int lanes_per_block, float* __restrict__ partial) {
