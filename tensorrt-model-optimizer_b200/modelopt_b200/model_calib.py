@@ -103,11 +103,13 @@ def max_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, **
             m._calibrator._checked = True
     finish_stats_collection(model)
     if distributed_sync and dist.is_available() and dist.is_initialized():
-        # quantizers calibrated outside the arena (custom calibrators): the reference's per-quantizer sync
+        # quantizers whose amax did not go through the arena — custom calibrators, and DISABLED quantizers that already
+        # hold an amax (AWQ's patched forwards calibrate the input quantizer per batch and leave it disabled): the
+        # reference's per-quantizer sync covers every quantizer with an ``_amax``, enabled or not (model_calib.py:117-130)
         group, ok = _dp_group(model)
         for m in model.modules():
-            if ok and isinstance(m, TensorQuantizer) and not m._disabled and getattr(m, "_amax", None) is not None \
-                    and not isinstance(getattr(m, "_calibrator", None), MaxCalibrator):
+            if ok and isinstance(m, TensorQuantizer) and getattr(m, "_amax", None) is not None \
+                    and (m._disabled or not isinstance(getattr(m, "_calibrator", None), MaxCalibrator)):
                 m.sync_amax_across_distributed_group(group)
     _finalize_with_shared_state(model)
 

@@ -89,6 +89,27 @@ def _quantize_sync(rank, world):
         assert q._if_quant and not q._if_calib
 
 
+def _disabled_amax_sync(rank, world):
+    """A quantizer that already holds an amax but is disabled when max_calibrate runs (AWQ's patched forwards leave the
+    input quantizers like that) still takes part in the all-reduce(MAX), as in the reference (model_calib.py:117-130)."""
+    import modelopt_b200 as mtq
+    from modelopt_b200.model_calib import max_calibrate
+    from torch import nn
+
+    m = nn.Sequential(nn.Linear(8, 8))
+    mtq.replace_quant_module(m)
+    mtq.set_quantizer_by_cfg(m, mtq.INT8_DEFAULT_CFG["quant_cfg"])
+    iq, wq = m[0].input_quantizer, m[0].weight_quantizer
+    iq.amax = torch.tensor(2.0 + rank)
+    iq.disable()
+    wq.disable()  # nothing left for the arena; no kernel runs
+    max_calibrate(m, lambda mod: None, distributed_sync=True)
+    assert float(iq.amax) == 2.0 + world - 1 and iq._disabled
+    iq.amax = torch.tensor(5.0 - rank)
+    max_calibrate(m, lambda mod: None, distributed_sync=False)
+    assert float(iq.amax) == 5.0 - rank
+
+
 def _hist_sync(rank, world):
     import modelopt_b200 as mtq
     from modelopt_b200.calib import HistogramCalibrator
@@ -140,6 +161,6 @@ def _hessian_sync(rank, world):
     assert all(torch.equal(t, gathered[0]) for t in gathered)  # bit-identical on every rank
 
 
-@pytest.mark.parametrize("fn", ["_arena_sync", "_quantize_sync", "_hist_sync", "_hessian_sync"])
+@pytest.mark.parametrize("fn", ["_arena_sync", "_quantize_sync", "_hist_sync", "_hessian_sync", "_disabled_amax_sync"])
 def test_world_size_2(fn):
     _spawn(fn)
