@@ -45,20 +45,30 @@ __global__ void __launch_bounds__(kThreads) block_hessian_kernel(const T* __rest
   for (int i = 0; i < 8; ++i)
 #pragma unroll
     for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
-  for (int64_t tb = t0; tb < t1; tb += kHTok) {
+  // the next tile's vectors are fetched into registers while this tile is multiplied: with two CTAs per SM the load
+  // latency (about as long as a tile's FMAs) was exposed once per tile
+  V32 pre[LOADS];
+  auto fetch = [&](int64_t tb) {
 #pragma unroll
     for (int l = 0; l < LOADS; ++l) {
       const int v = tid + l * kThreads, r = v / VPR, cv = v % VPR;
       const int64_t t = tb + r, c = col0 + (int64_t)cv * E;
-      V32 d;
-      if (t < t1 && c < cin) d = ld_stream(reinterpret_cast<const V32*>(x + t * cin + c));
+      if (t < t1 && c < cin) pre[l] = ld_stream(reinterpret_cast<const V32*>(x + t * cin + c));
       else {
 #pragma unroll
-        for (int k = 0; k < 8; ++k) d.w[k] = 0u;
+        for (int k = 0; k < 8; ++k) pre[l].w[k] = 0u;
       }
-      *reinterpret_cast<V32*>(&tile[r][cv * E]) = d;
+    }
+  };
+  if (t0 < t1) fetch(t0);
+  for (int64_t tb = t0; tb < t1; tb += kHTok) {
+#pragma unroll
+    for (int l = 0; l < LOADS; ++l) {
+      const int v = tid + l * kThreads, r = v / VPR, cv = v % VPR;
+      *reinterpret_cast<V32*>(&tile[r][cv * E]) = pre[l];
     }
     __syncthreads();
+    if (tb + kHTok < t1) fetch(tb + kHTok);
 #pragma unroll 2
     for (int r = 0; r < kHTok; ++r) {
       float a[8], b[8];
