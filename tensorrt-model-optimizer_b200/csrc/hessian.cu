@@ -202,10 +202,14 @@ __global__ void __launch_bounds__(kThreads) hessian_sweep_kernel(const T* __rest
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const float4 h = hr[q];
-        hdw[4 * q + 0] = __fmaf_rn(dw[i], h.x, hdw[4 * q + 0]);
-        hdw[4 * q + 1] = __fmaf_rn(dw[i], h.y, hdw[4 * q + 1]);
-        hdw[4 * q + 2] = __fmaf_rn(dw[i], h.z, hdw[4 * q + 2]);
-        hdw[4 * q + 3] = __fmaf_rn(dw[i], h.w, hdw[4 * q + 3]);
+        // packed fp32: two columns per instruction, each half an fma.rn (same bits, half the issue slots)
+        asm("{ .reg .b64 A, B, C, D, E;\n"
+            "  mov.b64 A, {%4, %4}; mov.b64 B, {%5, %6}; mov.b64 C, {%0, %1};\n"
+            "  mov.b64 D, {%7, %8}; mov.b64 E, {%2, %3};\n"
+            "  fma.rn.f32x2 C, A, B, C; fma.rn.f32x2 E, A, D, E;\n"
+            "  mov.b64 {%0, %1}, C; mov.b64 {%2, %3}, E; }"
+            : "+f"(hdw[4 * q + 0]), "+f"(hdw[4 * q + 1]), "+f"(hdw[4 * q + 2]), "+f"(hdw[4 * q + 3])
+            : "f"(dw[i]), "f"(h.x), "f"(h.y), "f"(h.z), "f"(h.w));
       }
     }
     float loss = 0.f;
