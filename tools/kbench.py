@@ -81,8 +81,13 @@ def main():
         del xf
         import time as _t
         for m, kw in (("percentile", {}), ("mse", {}), ("entropy", {})):
-            torch.cuda.synchronize(); t0 = _t.perf_counter(); v = hc.compute_amax(m, **kw); torch.cuda.synchronize()
-            print(f"hist search {m:10s} ({hc._counts.numel()} bins): {(_t.perf_counter() - t0) * 1e3:8.2f} ms -> {float(v):.4f}", flush=True)
+            best = None  # the first call pays the lazy load of the kernel's module: report the best of three
+            for _ in range(3):
+                torch.cuda.synchronize(); t0 = _t.perf_counter(); v = hc.compute_amax(m, **kw); torch.cuda.synchronize()
+                dt = (_t.perf_counter() - t0) * 1e3
+                first = dt if best is None else first
+                best = dt if best is None else min(best, dt)
+            print(f"hist search {m:10s} ({hc._counts.numel()} bins): {best:8.2f} ms (first call {first:.2f}) -> {float(v):.4f}", flush=True)
         from modelopt_b200.qtensor import NVFP4QTensor
         sf2 = am / 2688.0
         report("nvfp4 pack (codes + e4m3 scales)", 2.5625 * n, lambda: ops.nvfp4_pack(x, 16, sf2))
