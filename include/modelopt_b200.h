@@ -161,6 +161,18 @@ int64_t mo_hist_entropy_scratch_bytes(int64_t nbins, int stride, int start_bin);
 int mo_hist_entropy(const uint64_t* counts, int64_t nbins, int num_bits, int is_unsigned, int stride,
                     int start_bin, void* scratch, int32_t* idx_out, void* stream);
 
+/* mo_hist_entropy for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid
+ * cudaMalloc).  NO counterpart in the reference.  Same search, same
+ * result as mo_hist_entropy; the scratch is a fixed file-scope device array inside the library (1.5 MiB, held by
+ * every GPU that loads the library until the process exits), so the call performs no cudaMalloc / cudaFree and calls
+ * no allocating library routine.  Limit: nbins <= mo_hist_entropy_static_max_bins() (65536); more returns
+ * MO_ERR_ARG with a message - use mo_hist_entropy with your own scratch then.  All calls on one device share the
+ * array (it keeps the last call's contents; nothing in it needs to start at zero): calls that overlap on the GPU
+ * (different streams, parallel graph branches) race - serialise them. */
+int64_t mo_hist_entropy_static_max_bins(void);
+int mo_hist_entropy_static(const uint64_t* counts, int64_t nbins, int num_bits, int is_unsigned, int stride,
+                           int start_bin, int32_t* idx_out, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * NVFP4 real-quant packer (row a16): replaces NVFP4QTensor.quantize / dequantize
  * (qtensor/nvfp4_tensor.py:253-407) and the Triton fp4_dequantize (gemm/fp4_kernel.py:54-190).

@@ -269,3 +269,64 @@ extern "C" int mo_hist_entropy(const uint64_t* counts, int64_t nbins, int num_bi
   argmin_kernel<<<1, kSearchThreads, 0, s>>>(kl, ncand, 1, idx_out);
   return check_launch("mo_hist_entropy");
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// mo_hist_entropy_static: the same search for callers that cannot allocate (CUDA graph capture, serving loops that
+// forbid cudaMalloc).  No counterpart in the reference.  The scratch
+// (h, suffix sums, one KL word per candidate) lives in a file-scope device array of fixed size, so the call performs
+// no cudaMalloc / cudaFree and calls no allocating library routine.  Every GPU that loads the library holds the
+// array (kStaticEntropyBytes = 1.5 MiB) until the process exits.
+//
+// In host code `g_entropy_scratch` is only a host-side stand-in for the symbol, not a device address: its device
+// address is looked up once per device (with that device current) by cudaGetSymbolAddress and cached.
+//
+// All calls on a device share the array and it keeps the last call's contents.  Nothing in it has to start at zero:
+// the prep kernel rewrites h[0..nbins) and suffix[0..nbins], and every candidate's KL word is written before the
+// argmin reads it.  Calls that overlap on the GPU (different streams, or graph branches) race on it: serialise them.
+// ---------------------------------------------------------------------------------------------------------------------
+namespace mo {
+constexpr int64_t kStaticEntropyMaxBins = 65536;
+constexpr int64_t kStaticEntropyBytes = (3 * kStaticEntropyMaxBins + 2) * 8;  // h + suffix(+1) + one double per candidate
+static __device__ __align__(256) unsigned char g_entropy_scratch[kStaticEntropyBytes];
+
+constexpr int kMaxDevices = 64;
+static void* g_entropy_scratch_ptr[kMaxDevices];  // device address of the array, per device ordinal (0 = not looked up)
+static std::mutex g_entropy_scratch_mu;
+
+// device address of g_entropy_scratch on the CURRENT device
+static int static_entropy_scratch(void** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { set_error("mo_hist_entropy_static: cudaGetDevice: %s", cudaGetErrorString(e)); return (int)e; }
+  if (dev < 0 || dev >= kMaxDevices) { set_error("mo_hist_entropy_static: device ordinal %d out of range", dev); return MO_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(g_entropy_scratch_mu);
+  if (!g_entropy_scratch_ptr[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_entropy_scratch);
+    if (e != cudaSuccess || !p) {
+      set_error("mo_hist_entropy_static: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+      return e != cudaSuccess ? (int)e : MO_ERR_ARG;
+    }
+    g_entropy_scratch_ptr[dev] = p;
+  }
+  *out = g_entropy_scratch_ptr[dev];
+  return MO_OK;
+}
+}  // namespace mo
+
+extern "C" int64_t mo_hist_entropy_static_max_bins(void) { return kStaticEntropyMaxBins; }
+
+extern "C" int mo_hist_entropy_static(const uint64_t* counts, int64_t nbins, int num_bits, int is_unsigned, int stride,
+                                      int start_bin, int32_t* idx_out, void* stream) {
+  if (!counts || !idx_out) { set_error("mo_hist_entropy_static: NULL pointer"); return MO_ERR_NULL; }
+  if (nbins < 1 || nbins > kStaticEntropyMaxBins ||
+      mo_hist_entropy_scratch_bytes(nbins, stride < 1 ? 1 : stride, start_bin < 0 ? 0 : start_bin) > kStaticEntropyBytes) {
+    set_error("mo_hist_entropy_static: nbins = %lld exceeds the static scratch (at most %lld bins); use mo_hist_entropy "
+              "with a caller-provided scratch buffer", (long long)nbins, (long long)kStaticEntropyMaxBins);
+    return MO_ERR_ARG;
+  }
+  void* scratch = nullptr;
+  const int rc = static_entropy_scratch(&scratch);
+  if (rc != MO_OK) return rc;
+  return mo_hist_entropy(counts, nbins, num_bits, is_unsigned, stride, start_bin, scratch, idx_out, stream);
+}

@@ -39,6 +39,8 @@ SIGNATURES = {
     "mo_hist_mse": [_p, _p, _i64, _i, _i, _i, _i, _i, _i, _p, _p, _p],
     "mo_hist_entropy_scratch_bytes": [_i64, _i, _i],
     "mo_hist_entropy": [_p, _i64, _i, _i, _i, _i, _p, _p, _p],
+    "mo_hist_entropy_static_max_bins": [],
+    "mo_hist_entropy_static": [_p, _i64, _i, _i, _i, _i, _p, _p],
     "mo_nvfp4_pack": [_p, _i64, _i, _i, _p, _p, _p, _p, _p],
     "mo_nvfp4_unpack": [_p, _p, _p, _i64, _i, _i, _i, _p, _p],
     "mo_nvfp4_fp8_scale_sweep": [_p, _i64, _i, _i, _p, _p, _i, _p],
@@ -105,7 +107,7 @@ def load() -> C.CDLL:
     for name, argtypes in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is not exported
         fn.argtypes = argtypes
-        fn.restype = _i64 if name.endswith("_bytes") else _i
+        fn.restype = _i64 if name.endswith(("_bytes", "_max_bins")) else _i
     lib.mo_last_error.argtypes = []
     lib.mo_last_error.restype = C.c_char_p
     if lib.mo_abi_version() != ABI_VERSION:

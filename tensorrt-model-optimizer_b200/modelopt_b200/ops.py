@@ -497,6 +497,23 @@ def hist_entropy_index(counts, num_bits, unsigned, stride=1, start_bin=128):
     return idx
 
 
+def hist_entropy_index_static(counts, num_bits, unsigned, out, stride=1, start_bin=128):
+    """`hist_entropy_index` for callers that cannot allocate (CUDA graph capture, serving loops): the scratch is a fixed
+    device array inside the library (`mo_hist_entropy_static`; at most `mo_hist_entropy_static_max_bins()` = 65536
+    bins), and the result goes to the caller's `out` (device int32[1]).  Nothing is allocated here, by torch or by the
+    library.  Calls that overlap on the GPU share the scratch and race: keep them on one stream."""
+    _cuda(counts, "hist_entropy_index_static")
+    _cuda(out, "hist_entropy_index_static")
+    if out.dtype != torch.int32 or out.numel() < 1:
+        raise TypeError("out must be a device int32 tensor with at least one element")
+    with _dev(counts):
+        _launched(_lib.load().mo_hist_entropy_static(counts.data_ptr(), counts.numel(), int(num_bits),
+                                                     int(bool(unsigned)), int(stride), int(start_bin), out.data_ptr(),
+                                                     _stream(counts)),
+                  "mo_hist_entropy_static", n=3)
+    return out
+
+
 # ------------------------------------------------------------------------------------------------
 # NVFP4 packer (csrc/pack_nvfp4.cu)
 # ------------------------------------------------------------------------------------------------
