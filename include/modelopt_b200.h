@@ -426,7 +426,11 @@ int mo_amax_host(const void* x, int64_t n, int dtype, float* amax_out);
  * forward, tensor_quantizer.py:1181-1200; equal to mo_amax_host then mo_qdq_*_host per tensor): running_amax[i] =
  * max(running_amax[i], amax(x_i)), y_i = fake-quant(x_i) under it.  kind 0 = NVFP4 dynamic (`block`), 1 = FP8 per tensor.
  * Each tensor crosses the bus once per direction (it stays resident on the device between its amax and its fake-quant) and
- * the upload of tensor i+1 overlaps the fake-quant + download of tensor i.  Host pointers should be pinned. */
+ * the upload of tensor i+1 overlaps the fake-quant + download of tensor i.  Host pointers should be pinned.
+ * xs[i] may also be a DEVICE pointer (a weight that already lives on the GPU: read in place, no copy).  ys[i] may be a
+ * device pointer (written in place) or NULL = calibration-only: the fake-quantized tensor stays on the device (in the
+ * pipeline's buffer, for the consumer kernel) and only running_amax[i] returns - what max_calibrate
+ * (model_calib.py:311-498) needs back.  One pipeline per device ordinal (the current device's). */
 int mo_calib_qdq_host_batch(int n_tensors, const void* const* xs, void* const* ys, const int64_t* rows, const int64_t* cols,
                             int dtype, float* running_amax, int kind, int block, int numerics);
 

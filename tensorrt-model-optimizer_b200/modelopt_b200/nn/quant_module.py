@@ -331,7 +331,7 @@ class _QuantLinear(QuantLinearConvBase):
                 out = ops.linear_qdq(input, self.quantized_weight(), self.bias, q._amax, fmt, q._narrow_range,
                                      prescale=q.pre_quant_scale)
             else:
-                out = ops.linear(q(input), self.quantized_weight(), self.bias)
+                out = ops.plain_linear(q(input), self.quantized_weight(), self.bias)
             return self.output_quantizer(out)
         return super().forward(input, *args, **kwargs)
 

@@ -376,19 +376,27 @@ def amax_host(x: torch.Tensor) -> float:
     return out.value
 
 
-def calib_qdq_host_batch(xs, running_amax, kind="nvfp4", block=16, numerics=None, outs=None):
-    """Collect + fake-quant of a batch of host tensors in one pipelined call: running_amax[i] (list of floats, updated in
-    place) = max(running_amax[i], max|x_i|) and y_i = fake-quant(x_i) under it.  Every tensor crosses the bus once per
-    direction; the upload of x_{i+1} overlaps the fake-quant + download of y_i.  Returns the list of outputs."""
+def calib_qdq_host_batch(xs, running_amax, kind="nvfp4", block=16, numerics=None, outs=None, download=True):
+    """Collect + fake-quant of a batch of tensors in one pipelined call: running_amax[i] (list of floats, updated in
+    place) = max(running_amax[i], max|x_i|) and y_i = fake-quant(x_i) under it.  A HOST tensor crosses the bus once per
+    direction (the upload of x_{i+1} overlaps the fake-quant + download of y_i); a CUDA tensor among `xs` (weights that
+    live on the GPU) is read in place.  ``download=False`` (or a ``None`` entry in ``outs``) is the calibration-only
+    form: the fake-quantized tensor stays on the device and only the amax comes back.  Returns the list of outputs."""
     n = len(xs)
     assert len(running_amax) == n
     for t in xs:
-        _host(t, "calib_qdq_host_batch")
-    ys = [torch.empty_like(t) for t in xs] if outs is None else outs
+        if not t.is_cuda:
+            _host(t, "calib_qdq_host_batch")
+        elif not t.is_contiguous():
+            raise ValueError("modelopt_b200.calib_qdq_host_batch: expected contiguous tensors")
+    if outs is None:
+        ys = [torch.empty_like(t) if download else None for t in xs]
+    else:
+        ys = list(outs)
     code = _code(xs[0])
     assert all(_code(t) == code for t in xs), "one dtype per batch"
     xp = (C.c_void_p * n)(*[t.data_ptr() for t in xs])
-    yp = (C.c_void_p * n)(*[t.data_ptr() for t in ys])
+    yp = (C.c_void_p * n)(*[t.data_ptr() if t is not None else None for t in ys])
     cols = [t.shape[-1] if t.dim() else 1 for t in xs]
     rows = (C.c_int64 * n)(*[t.numel() // max(c, 1) for t, c in zip(xs, cols)])
     colsa = (C.c_int64 * n)(*cols)
@@ -1035,6 +1043,23 @@ LINEAR_PAIR = {"min_rows": 512}
 def _pair_fn(M, pair):
     use = pair if pair is not None else (LINEAR_PAIR["min_rows"] is not None and M >= LINEAR_PAIR["min_rows"])
     return _lib.load().mo_linear_pair if use else _lib.load().mo_linear
+
+
+# Which GEMM a quantized linear's PLAIN product (no fused prologue / loss epilogue / real-quant operands) runs on:
+#   "tcgen05" = this library's kernels (mo_linear / mo_linear_pair), "cublas" = torch's F.linear, "auto" = whichever was
+#   measured faster for the shape on B200.  Inside a Llama-3-8B forward cuBLAS's nvjet 256x256 pair kernel sustains ~1600
+#   TFLOP/s against ~1330 for mo_linear_pair (profiles/r02_model_profile.txt), so "auto" keeps a plain GEMM on the library
+#   the reference itself calls (quant_linear.py:38-53 -> F.linear); the tcgen05 kernels carry what cuBLAS cannot do
+#   (loss epilogue, QDQ prologue, NVFP4 / FP8 real-quant operands).  Override: MODELOPT_B200_PLAIN_GEMM=tcgen05|cublas|auto.
+PLAIN_GEMM = {"backend": os.environ.get("MODELOPT_B200_PLAIN_GEMM", "auto").lower()}
+
+
+def plain_linear(x, weight, bias=None):
+    """The quantized linear's plain product, on the backend PLAIN_GEMM selects (operands already fake-quantized)."""
+    be = PLAIN_GEMM["backend"]
+    if be == "tcgen05":
+        return linear(x, weight, bias)
+    return torch.nn.functional.linear(x, weight, bias)
 
 
 def linear(x, weight, bias=None, out=None, pair=None):

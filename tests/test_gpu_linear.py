@@ -149,15 +149,22 @@ def test_quant_linear_small_batch_uses_one_kernel():
         n0 = ops.LAUNCHES[0]
         y = m(x)
         assert ops.LAUNCHES[0] - n0 == 2          # one fused kernel per linear
-        old = dict(ops.FUSED_PROLOGUE)
+        old, old_gemm = dict(ops.FUSED_PROLOGUE), dict(ops.PLAIN_GEMM)
         ops.FUSED_PROLOGUE["max_rows"] = 0
         try:
+            ops.PLAIN_GEMM["backend"] = "tcgen05"
             n0 = ops.LAUNCHES[0]
             y2 = m(x)
-            assert ops.LAUNCHES[0] - n0 == 4      # input QDQ + GEMM per linear
+            assert ops.LAUNCHES[0] - n0 == 4      # input QDQ + this library's GEMM per linear
+            ops.PLAIN_GEMM["backend"] = "cublas"
+            n0 = ops.LAUNCHES[0]
+            y3 = m(x)
+            assert ops.LAUNCHES[0] - n0 == 2      # input QDQ per linear; the plain product runs in cuBLAS
         finally:
             ops.FUSED_PROLOGUE.update(old)
+            ops.PLAIN_GEMM.update(old_gemm)
     assert torch.equal(y, y2)
+    assert (y.float() - y3.float()).abs().max().item() <= 2.0 ** -7 * y.float().abs().max().item()
 
 
 @pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16])

@@ -396,3 +396,28 @@ def test_calib_qdq_host_batch_equals_separate_calls(kind):
     again = list(got_am)
     ops.calib_qdq_host_batch(xs, again, kind)
     assert again == got_am
+
+
+@pytest.mark.parametrize("kind", ["nvfp4", "fp8"])
+def test_calib_qdq_host_batch_device_inputs_and_calibration_only(kind):
+    """Device-resident inputs are read in place, a device output is written in place, a NULL output (calibration-only)
+    returns only the running amax: all three agree with the all-host form."""
+    from modelopt_b200 import ops
+
+    torch.manual_seed(5)
+    shapes = [(300, 256), (1024, 4096), (77, 1024), (513, 128), (64, 512)]
+    xs = [(torch.randn(s) * (i + 1)).to(torch.bfloat16).pin_memory() for i, s in enumerate(shapes)]
+    running = [0.0, 100.0, 0.5, 0.0, 3.0]
+    want_am = list(running)
+    want = ops.calib_qdq_host_batch(xs, want_am, kind)
+    # tensors 1 and 3 live on the device; output 1 is a device tensor, outputs 2 and 4 are not wanted back
+    mixed = [x.cuda() if i in (1, 3) else x for i, x in enumerate(xs)]
+    outs = [torch.empty_like(xs[0]), torch.empty_like(mixed[1]), None, torch.empty_like(xs[3]), None]
+    got_am = list(running)
+    got = ops.calib_qdq_host_batch(mixed, got_am, kind, outs=outs)
+    assert got_am == want_am
+    for i in (0, 1, 3):
+        assert torch.equal(got[i].cpu().view(torch.int16), want[i].view(torch.int16)), i
+    only_am = list(running)
+    assert ops.calib_qdq_host_batch(mixed, only_am, kind, download=False) == [None] * 5
+    assert only_am == want_am
