@@ -140,6 +140,32 @@ int mo_amax(const void* x, int64_t outer, int64_t axis_size, int64_t inner, int 
 int mo_hist(const void* x, int64_t n, int dtype, const float* range_max, int64_t nbins, uint64_t* counts,
             uint32_t* amax_bits, int skip_zeros, void* stream);
 
+/* HistogramCalibrator.collect (histogram.py:77-130) WITHOUT a host round trip per batch.  The calibrator's parameters live
+ * in `state` (device int32[MO_HIST_STATE_WORDS], zero-initialised by the caller) and `counts` has a fixed `capacity`
+ * (bins beyond the current nbins stay zero).  Per batch the caller runs mo_hist_collect_begin, then - data-parallel
+ * calibration only - an all-reduce(MAX) over state[MO_HIST_BATCH_AMAX] (one word), then mo_hist_collect_end:
+ *   first = 1 : begin = max|x|;  end = nbins := init_bins, range := that max (histogram.py:116-118), bin x.
+ *   first = 0 : begin = bin x under the current range and fold max|x| in the same read;  end = if the max exceeds the
+ *               range, grow it exactly like histogram.py:121-126 (num_bins = ceil(x_max / width), range = last edge of
+ *               arange(0, x_max + width, width); numerics = MO_NUMERICS_CPU evaluates arange like the CPU kernel, in
+ *               fp64) and move the batch from the old bins to the new ones (two more reads of x, only on such batches).
+ * With the all-reduce every rank takes the same decisions, so its counts are bin-compatible with every other rank's and
+ * their SUM equals one process calibrating on the concatenated batches.  A range needing more than `capacity` bins, or
+ * a non-finite max, sets a flag in state[MO_HIST_FLAGS] and freezes the state (later launches are no-ops); the caller
+ * reads the state back whenever it likes (compute_amax does).  smem_bins_hint: how many bins to keep in shared-memory
+ * counters (any value is correct; nbins or a little more is fastest; 0 = capacity). */
+enum {
+  MO_HIST_NBINS = 0, MO_HIST_RANGE_MAX = 1, MO_HIST_WIDTH = 2, MO_HIST_LAST_END = 3, MO_HIST_FLAGS = 4,
+  MO_HIST_FIRST_AMAX = 5, MO_HIST_BATCH_AMAX = 6, MO_HIST_GROWN = 7, MO_HIST_OLD_NBINS = 8, MO_HIST_OLD_RANGE_MAX = 9,
+  MO_HIST_BATCHES = 10, MO_HIST_CAPACITY = 11, MO_HIST_STATE_WORDS = 16
+};
+#define MO_HIST_FLAG_OVERFLOW 1   /* the range would need more than `capacity` bins */
+#define MO_HIST_FLAG_NONFINITE 2  /* max|x| was inf or NaN (torch.histc raises "range ... is not finite") */
+int mo_hist_collect_begin(const void* x, int64_t n, int dtype, int32_t* state, uint64_t* counts, int64_t capacity,
+                          int64_t smem_bins_hint, int skip_zeros, int first, void* stream);
+int mo_hist_collect_end(const void* x, int64_t n, int dtype, int32_t* state, uint64_t* counts, int64_t capacity,
+                        int64_t smem_bins_hint, int skip_zeros, int first, int init_bins, int numerics, void* stream);
+
 /* _compute_amax_percentile (histogram.py:328-343): *idx_out (device) = searchsorted(cumsum(hist/total),
  * percentile/100) in fp64, numpy's summation order; the amax is edges[idx]. */
 int mo_hist_percentile(const uint64_t* counts, int64_t nbins, double percentile, int32_t* idx_out,

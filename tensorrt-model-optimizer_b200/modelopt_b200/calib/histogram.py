@@ -1,18 +1,26 @@
 """HistogramCalibrator on the B200 path (interface of modelopt/torch/quantization/calib/histogram.py:35-343).
 
 ``collect`` keeps the reference's contract — 2048 bins over [0, max|x|] on the first batch, the range grows in
-whole bin widths afterwards, old counts are added to the prefix of the new histogram — but does it in one or
-two reads of the bf16 tensor instead of the reference's abs / float-copy / max / histc chain:
+whole bin widths afterwards, old counts are added to the prefix of the new histogram — without the reference's
+abs / float-copy / max / histc chain and WITHOUT a host round trip per batch (the reference syncs twice per collect,
+histogram.py:79, :121-123):
 
-* steady state: ONE kernel (``mo_hist``) adds the bins of |x| under the current range to the running counts and
-  folds max|x| in the same pass (plus a 4-byte memset and one 4-byte read); only if that max exceeded the range (the
-  reference's ``x_max > edges[-1]``, a host decision there too) is the batch taken out again and re-binned with the
-  grown range;
-* first batch: an amax pass fixes the range, then one binning pass.
+* the calibrator's parameters (bin count, range, width, flags) live in a 16-word device state and the counts in a device
+  buffer of fixed capacity (``headroom`` x ``num_bins`` bins); ``collect`` enqueues kernels and returns;
+* steady state: ONE read of the tensor bins |x| under the current range and folds max|x| in the same pass; a one-thread
+  kernel then takes the reference's ``x_max > edges[-1]`` decision on the device, and only a batch that grows the range
+  is read again (taken out of the old bins, put into the new ones);
+* data-parallel calibration (``dp_group`` set by ``enable_stats_collection``): the batch maximum is all-reduced(MAX)
+  between those two steps — one word, stream-ordered — so every rank takes the same decisions, its bins are the other
+  ranks' bins, and the SUM of the ranks' counts (``model_calib.sync_histograms``) is bit-identical to one process
+  calibrating on the concatenated batches.  New behaviour: the reference does not synchronise histograms
+  (calib/histogram.py:158-163); with one rank nothing changes.
 
 Counts are exact int64 (the reference's fp32 ``torch.histc`` stops counting at 2^24 per bin); ``_calib_hist``
-is exposed as fp32 like the reference's.  Bin edges are built with the same ``torch.linspace`` / ``torch.arange``
-calls as the reference so that they are bit-identical.
+is exposed as fp32 like the reference's.  Bin edges are rebuilt on demand with the same ``torch.linspace`` / ``torch.arange``
+calls as the reference so that they are bit-identical.  A range that would need more than ``headroom * num_bins`` bins, or
+a non-finite maximum (``torch.histc`` raises there), freezes the device state and is reported by the next state read
+(at the latest by ``compute_amax``).
 
 ``compute_amax`` runs the percentile / mse / entropy searches on the device (``csrc/hist_search.cu``) and looks the
 amax up in the edge array exactly like the reference.  ``method="mse"`` reproduces the reference's mis-slotted
@@ -31,27 +39,42 @@ from .calibrator import _Calibrator
 
 __all__ = ["HistogramCalibrator", "calibrate_weights"]
 
+# include/modelopt_b200.h MO_HIST_*
+_NBINS, _RANGE_MAX, _WIDTH, _LAST_END, _FLAGS, _FIRST_AMAX, _BATCH_AMAX = 0, 1, 2, 3, 4, 5, 6
+_STATE_WORDS = 16
+_FLAG_OVERFLOW, _FLAG_NONFINITE = 1, 2
+
 
 class HistogramCalibrator(_Calibrator):
     def __init__(self, num_bits=8, axis=None, unsigned=False, num_bins=2048, grow_method=None, skip_zeros=False,
-                 torch_hist=True):
+                 torch_hist=True, headroom=32):
         super().__init__(num_bits, axis, unsigned)
-        self._num_bins = num_bins
+        self._init_bins = num_bins
         self._skip_zeros = skip_zeros
-        self._calib_bin_edges = None
-        self._counts = None  # int64 device tensor
-        self._range_cache = None  # (edges object, device range_max, its bit pattern, amax scratch word)
+        self._headroom = headroom
+        self._state = None      # int32[16] device: bin count, range, width, flags (include/modelopt_b200.h MO_HIST_*)
+        self._buf = None        # int64[capacity] device counts; bins beyond the current bin count are zero
+        self._snap = None       # last host copy of the state: (list of 16 ints)
+        self._pending = None    # event of an asynchronous state read-back into self._host
+        self._host = None       # pinned int32[16]
+        self._snap_valid = False  # self._snap is the CURRENT device state (nothing was enqueued since it was read)
+        self._edges_cache = None
+        self._override = None   # (counts, edges) set by hand (tests, external restore)
+        self._synced = False    # counts already summed over the data-parallel group
         self._torch_hist = torch_hist
+        # data-parallel group whose ranks calibrate together: False = none; None = the default (world) group
+        self.dp_group = False
         # "cpu": build grown bin edges with torch.arange on the CPU (what the reference computes for CPU tensors;
         # CPU arange evaluates start + i*step in fp64, CUDA arange in fp32, so edges can differ in the last bit)
         self.numerics = None
         if axis is not None:
             raise NotImplementedError("Calibrator histogram collection only supports per tensor scaling")
 
-    # the reference's attribute: fp32 counts
-    @property
-    def _calib_hist(self):
-        return None if self._counts is None else self._counts.to(torch.float32)
+    # ---- device state ------------------------------------------------------------------------------------------------
+    def _group_size(self):
+        if self.dp_group is False or not (dist.is_available() and dist.is_initialized()):
+            return 1
+        return dist.get_world_size(self.dp_group)
 
     @torch.no_grad()
     def collect(self, x):
@@ -60,66 +83,125 @@ class HistogramCalibrator(_Calibrator):
         x = x.detach()
         if x.dtype == torch.float64:
             x = x.float()
-        dev = x.device
-        if self._counts is None:
-            amax_bits = torch.zeros(1, dtype=torch.int32, device=dev)
-            ops.amax_into(x, 1, 1, x.numel(), amax_bits)
-            x_max = amax_bits.view(torch.float32)
-            self._check_finite(x_max)
-            counts = torch.zeros(self._num_bins, dtype=torch.int64, device=dev)
-            ops.hist_into(x, x_max, counts, None, self._skip_zeros)
-            self._counts = counts
-            self._calib_bin_edges = torch.linspace(0, x_max[0], self._num_bins + 1)  # histogram.py:118 (CPU tensor)
+        if x.numel() == 0:
             return
-        edges = self._calib_bin_edges
-        cache = self._range_cache
-        if cache is None or cache[0] is not edges or cache[1].device != dev:
-            range_max = edges[-1:].to(device=dev, dtype=torch.float32)
-            cache = self._range_cache = (edges, range_max, int(range_max.view(torch.int32).item()),
-                                         torch.zeros(1, dtype=torch.int32, device=dev))
-        _, range_max, range_bits, amax_bits = cache
-        # Steady state: ONE kernel adds this batch straight into the running counts with the current range and folds
-        # max|x| in the same read; the host then looks at one word (the reference's `x_max > edges[-1]` branch, :121,
-        # is a host decision too).  fp32 bit patterns of non-negative values order like the values, NaN above +inf.
-        amax_bits.zero_()
-        ops.hist_into(x, range_max, self._counts, amax_bits, self._skip_zeros)
-        if int(amax_bits.item()) > range_bits:
-            x_max = amax_bits.view(torch.float32)
-            # the range grows (rare): take the speculative batch out again, then re-bin it with the new range
-            undo = torch.zeros_like(self._counts)
-            ops.hist_into(x, range_max, undo, None, self._skip_zeros)
-            self._counts -= undo
-            self._check_finite(x_max)
-            width = edges[1] - edges[0]
-            xm = x_max[0].to(width.device)
-            self._num_bins = int((xm / width).ceil().item())
-            cpu = ops._mode(self.numerics) == ops.MO_DIV_IEEE
-            self._calib_bin_edges = torch.arange(0, xm.cpu() + width.cpu() if cpu else xm + width,
-                                                 width.cpu() if cpu else width,
-                                                 device="cpu" if cpu else dev)  # :124-126
-            range_max = self._calib_bin_edges[-1:].to(dev).contiguous()
-            new = torch.zeros(self._num_bins, dtype=torch.int64, device=dev)
-            ops.hist_into(x, range_max, new, None, self._skip_zeros)
-            new[: self._counts.numel()] += self._counts
-            self._counts = new
+        x = x.contiguous()
+        self._override = None
+        first = self._state is None
+        if first:
+            self._state = torch.zeros(_STATE_WORDS, dtype=torch.int32, device=x.device)
+            self._buf = torch.zeros(self._init_bins * self._headroom, dtype=torch.int64, device=x.device)
+            self._snap = None
+        else:
+            self._poll()  # a finished read-back of an earlier batch: learn the bin count, report a frozen state
+        hint = self._hint()
+        ops.hist_collect_begin(x, self._state, self._buf, hint, self._skip_zeros, first)
+        if self._group_size() > 1:  # one word; every rank then takes the same grow / no-grow decision
+            dist.all_reduce(self._state[_BATCH_AMAX:_BATCH_AMAX + 1], op=dist.ReduceOp.MAX, group=self.dp_group)
+        ops.hist_collect_end(x, self._state, self._buf, hint, self._skip_zeros, first, self._init_bins, self.numerics)
+        self._synced = False
+        self._edges_cache = None
+        self._snap_valid = False
+        if self._pending is None:  # asynchronous read-back: 64 bytes, looked at by a later collect
+            if self._host is None:
+                self._host = torch.empty(_STATE_WORDS, dtype=torch.int32).pin_memory()
+            self._host.copy_(self._state, non_blocking=True)
+            self._pending = torch.cuda.Event()
+            self._pending.record()
+
+    def _hint(self):
+        """Bins to keep in shared-memory counters: the last bin count the host has seen (any value is correct)."""
+        return max(self._init_bins, self._snap[_NBINS] if self._snap else 0)
+
+    def _poll(self):
+        if self._pending is not None and self._pending.query():
+            self._snap = self._host.tolist()
+            self._pending = None
+            self._raise_if_frozen(self._snap)
+
+    def _raise_if_frozen(self, snap):
+        if snap[_FLAGS] & _FLAG_NONFINITE:  # what torch.histc raises in the reference's collect
+            raise RuntimeError("torch.histc: range of [0, inf or nan] is not finite (a batch's max|x| was inf or NaN)")
+        if snap[_FLAGS] & _FLAG_OVERFLOW:
+            raise RuntimeError(
+                f"modelopt_b200 HistogramCalibrator: the range grew beyond {self._headroom}x the first batch's "
+                f"({self._init_bins * self._headroom} bins of the first batch's width); batches from that point on were "
+                "not collected.  Construct the calibrator with a larger `headroom`.")
+
+    def _read_state(self):
+        """Blocking read of the device state (compute time, tests): list of 16 ints."""
+        if self._state is None:
+            return None
+        if not self._snap_valid or self._snap is None:
+            self._snap = self._state.tolist()
+            self._snap_valid = True
+            if self._pending is not None:
+                self._pending.synchronize()  # the pinned buffer is free again
+                self._pending = None
+        self._raise_if_frozen(self._snap)
+        return self._snap
 
     @staticmethod
-    def _check_finite(x_max):
-        v = float(x_max[0])
-        if v != v or v in (float("inf"), float("-inf")):
-            raise RuntimeError(f"torch.histc: range of [0, {v}] is not finite")
+    def _f32(bits: int) -> float:
+        return float(torch.tensor([bits], dtype=torch.int32).view(torch.float32)[0])
+
+    # ---- the reference's attributes -------------------------------------------------------------------------------------
+    @property
+    def _num_bins(self):
+        if self._override is not None:
+            return self._override[0].numel()
+        snap = self._read_state()
+        return self._init_bins if snap is None else snap[_NBINS]
+
+    @_num_bins.setter
+    def _num_bins(self, value):
+        self._init_bins = value
+
+    @property
+    def _counts(self):
+        if self._override is not None:
+            return self._override[0]
+        snap = self._read_state()
+        return None if snap is None else self._buf[: snap[_NBINS]]
+
+    @property
+    def _calib_hist(self):
+        c = self._counts
+        return None if c is None else c.to(torch.float32)
+
+    @property
+    def _calib_bin_edges(self):
+        if self._override is not None:
+            return self._override[1]
+        snap = self._read_state()
+        if snap is None:
+            return None
+        if self._edges_cache is None:
+            if snap[_LAST_END] == 0:  # never grown: histogram.py:118 (a CPU tensor in the reference too)
+                self._edges_cache = torch.linspace(0, self._f32(snap[_FIRST_AMAX]), snap[_NBINS] + 1)
+            else:                     # :124-126
+                cpu = ops._mode(self.numerics) == ops.MO_DIV_IEEE
+                self._edges_cache = torch.arange(0, self._f32(snap[_LAST_END]), self._f32(snap[_WIDTH]),
+                                                 device="cpu" if cpu else self._state.device)
+        return self._edges_cache
+
+    def set_histogram(self, counts, edges):
+        """Install a histogram by hand (restore, tests): later ``compute_amax`` calls use it; ``collect`` discards it."""
+        self._override = (counts, edges)
 
     def reset(self):
-        self._calib_bin_edges = None
-        self._counts = None
-        self._range_cache = None
+        if self._pending is not None:
+            self._pending.synchronize()
+        self._state = self._buf = self._snap = self._pending = self._edges_cache = self._override = None
+        self._synced = self._snap_valid = False
 
     def compute_amax(self, method: str, *, stride: int = 1, start_bin: int = 128, percentile: float = 99.99,
                      intended_mse: bool = False):
-        if dist.is_initialized():
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1 and not self._synced:
             warnings.warn(
-                "This method does not perform any synchronization across distributed processes. Use "
-                "modelopt_b200.model_calib.sync_histograms() or the same calibration data on every rank."
+                "This histogram was not synchronized across distributed processes (the reference never does, "
+                "calib/histogram.py:158-163). Use enable_stats_collection() / finish_stats_collection(), or "
+                "modelopt_b200.model_calib.sync_histograms(), or the same calibration data on every rank."
             )
         if self._counts is None and self._calib_bin_edges is None:
             return None
@@ -170,7 +252,7 @@ def calibrate_weights(model, method="percentile", perchannel=True, percentile=99
         chans = range(w.shape[0]) if perchannel else [slice(None)]
         amaxs = []
         for c in chans:
-            cal = HistogramCalibrator(q.num_bits, None, q.unsigned, num_bins=num_bins)
+            cal = HistogramCalibrator(q.num_bits, None, q.unsigned, num_bins=num_bins, headroom=1)  # one batch: no growth
             cal.collect(w[c].contiguous())
             amaxs.append(cal.compute_amax(method, percentile=percentile) if method == "percentile"
                          else cal.compute_amax(method))

@@ -38,8 +38,7 @@ def pack_real_quantize_weight(module: nn.Module, force_quantize: bool = False) -
                 if force_quantize:
                     q._dequantize = False
                 m._parameters["weight"] = QTensorWrapper(q(w.data))
-                m.__dict__.pop("_wq_cache", None)
-                m.__dict__.pop("_w4_cache", None)
+                m.invalidate_weight_cache()
                 n += 1
     return n
 

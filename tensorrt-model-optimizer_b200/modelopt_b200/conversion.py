@@ -41,7 +41,7 @@ def replace_quant_module(model: nn.Module, registry=QuantModuleRegistry):
     return model
 
 
-def _match(pattern: str | Callable, name: str, module, parent_class, model) -> bool:
+def _match(pattern: str | Callable, name: str, module, parent_class, model, parents=None) -> bool:
     if not isinstance(module, (TensorQuantizer, SequentialQuantizer)):
         return False
     if isinstance(pattern, str):
@@ -55,35 +55,54 @@ def _match(pattern: str | Callable, name: str, module, parent_class, model) -> b
         raise NotImplementedError(f"Unsupported type {type(pattern)}")
     if parent_class is None:
         return True
-    return isinstance(model.get_submodule(".".join(name.split(".")[:-1])), parent_class)
+    pname = name.rpartition(".")[0]
+    parent = parents[pname] if parents is not None else model.get_submodule(pname)
+    return isinstance(parent, parent_class)
 
 
-def set_quantizer_attributes_full(model, pattern, attributes, parent_class=None):
+class _QuantizerIndex:
+    """(name, quantizer) pairs of a model, listed ONCE per `set_quantizer_by_cfg` instead of one `named_modules()` walk of
+    the whole model per config entry (a Llama-3-8B has 1100 modules and a preset about 25 entries).  Entries are
+    refreshed in place when a quantizer object is swapped (TensorQuantizer <-> SequentialQuantizer)."""
+
+    def __init__(self, model):
+        self.model = model
+        self.parents = dict(model.named_modules())
+        self.items = [(n, m) for n, m in self.parents.items() if isinstance(m, (TensorQuantizer, SequentialQuantizer))]
+
+    def replace(self, name, module):
+        parent = self.parents[name.rpartition(".")[0]]
+        setattr(parent, name.rpartition(".")[2], module)
+        fresh = _QuantizerIndex(self.model)  # the children of the old / new object changed too; rare, so just re-list
+        self.parents, self.items = fresh.parents, fresh.items
+
+
+def set_quantizer_attributes_full(model, pattern, attributes, parent_class=None, _index=None):
     """Replace ALL attributes of the matched quantizers (unspecified fields revert to their defaults); a list of
     configs turns the quantizer into a SequentialQuantizer."""
     if not isinstance(attributes, (QuantizerAttributeConfig, list)):
         raise ValueError(f"Invalid type for attributes: {type(attributes)}")
-    for name, module in list(model.named_modules()):
-        if not _match(pattern, name, module, parent_class, model):
+    idx = _index if _index is not None else _QuantizerIndex(model)
+    for name, module in list(idx.items):  # snapshot: quantizers created by a replacement below are not visited
+        if idx.parents.get(name) is not module or not _match(pattern, name, module, parent_class, model, idx.parents):
             continue
         if isinstance(attributes, list):
             if not isinstance(module, SequentialQuantizer) or len(module) != len(attributes):
-                parent = model.get_submodule(".".join(name.split(".")[:-1]))
                 module = SequentialQuantizer(*(TensorQuantizer() for _ in attributes))
-                setattr(parent, name.split(".")[-1], module)
+                idx.replace(name, module)
             module.set_from_attribute_config(attributes)
         else:
             if isinstance(module, SequentialQuantizer):
-                parent = model.get_submodule(".".join(name.split(".")[:-1]))
                 module = TensorQuantizer()
-                setattr(parent, name.split(".")[-1], module)
+                idx.replace(name, module)
             module.set_from_attribute_config(attributes)
 
 
-def set_quantizer_attributes_partial(model, pattern, attributes: dict[str, Any], parent_class=None):
+def set_quantizer_attributes_partial(model, pattern, attributes: dict[str, Any], parent_class=None, _index=None):
     """Update only the given attributes of the matched quantizers."""
-    for name, module in model.named_modules():
-        if _match(pattern, name, module, parent_class, model):
+    idx = _index if _index is not None else _QuantizerIndex(model)
+    for name, module in idx.items:
+        if _match(pattern, name, module, parent_class, model, idx.parents):
             targets = module if isinstance(module, SequentialQuantizer) else [module]
             for q in targets:
                 q.set_from_attribute_config(attributes)
@@ -100,6 +119,7 @@ def set_quantizer_attribute(model, pattern, attribute, parent_class=None):
 def set_quantizer_by_cfg(model: nn.Module, quant_cfg):
     """Apply an ordered quant_cfg list: later entries override earlier ones; an entry with ``cfg`` is a complete
     replacement, an entry with only ``enable`` toggles."""
+    index = _QuantizerIndex(model)
     for entry in normalize_quant_cfg_list(quant_cfg):
         name, cfg, enable = entry["quantizer_name"], entry["cfg"], entry["enable"]
         pc = entry.get("parent_class")
@@ -111,15 +131,15 @@ def set_quantizer_by_cfg(model: nn.Module, quant_cfg):
         else:
             parent_class = None
         if cfg is None:
-            set_quantizer_attributes_partial(model, name, {"enable": enable}, parent_class)
+            set_quantizer_attributes_partial(model, name, {"enable": enable}, parent_class, index)
         elif isinstance(cfg, QuantizerAttributeConfig):
-            set_quantizer_attributes_full(model, name, cfg.model_copy(update={"enable": enable}), parent_class)
+            set_quantizer_attributes_full(model, name, cfg.model_copy(update={"enable": enable}), parent_class, index)
         elif isinstance(cfg, dict):
-            set_quantizer_attributes_full(model, name, QuantizerAttributeConfig(**cfg, enable=enable), parent_class)
+            set_quantizer_attributes_full(model, name, QuantizerAttributeConfig(**cfg, enable=enable), parent_class, index)
         else:
             attrs = [c.model_copy(update={"enable": enable}) if isinstance(c, QuantizerAttributeConfig)
                      else QuantizerAttributeConfig(**c, enable=enable) for c in cfg]
-            set_quantizer_attributes_full(model, name, attrs, parent_class)
+            set_quantizer_attributes_full(model, name, attrs, parent_class, index)
 
 
 @contextlib.contextmanager

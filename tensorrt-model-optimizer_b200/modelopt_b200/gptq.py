@@ -128,7 +128,7 @@ class GPTQHelper:
         self._blockwise_update(block_size)
         self.rel_mse = self._mse_error(hessian, w)
         w.data = self.weight.reshape(w.shape).to(w.dtype)
-        self.module.__dict__.pop("_wq_cache", None)
+        self.module.invalidate_weight_cache()
 
     def _blockwise_update(self, block_size):
         q = self.module.weight_quantizer

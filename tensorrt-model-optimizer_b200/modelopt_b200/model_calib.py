@@ -26,7 +26,7 @@ from .nn.tensor_quantizer import SequentialQuantizer, TensorQuantizer
 from .utils import is_quantized_linear
 
 __all__ = ["max_calibrate", "enable_stats_collection", "finish_stats_collection", "weight_only_quantize",
-           "disable_pre_quant_scale_and_resmooth", "sync_histograms"]
+           "disable_pre_quant_scale_and_resmooth", "sync_histograms", "sync_max_calibrators"]
 
 
 def weight_only_quantize(model: nn.Module):
@@ -41,8 +41,16 @@ def weight_only_quantize(model: nn.Module):
         seen.add(module)
 
 
-def enable_stats_collection(model: nn.Module, arena_pool: AmaxArenaPool | None = None):
-    """model_calib.py:1128-1141 (+ attach the shared amax arena to every max calibrator)."""
+def enable_stats_collection(model: nn.Module, arena_pool: AmaxArenaPool | None = None, distributed_sync: bool = True):
+    """model_calib.py:1128-1141 (+ attach the shared amax arena to every max calibrator, and tell every histogram
+    calibrator which data-parallel group it calibrates with: see `sync_histograms`)."""
+    from .calib import HistogramCalibrator
+
+    hist_group = False
+    if distributed_sync and dist.is_available() and dist.is_initialized():
+        group, ok = _dp_group(model)
+        if ok and dist.get_world_size(group) > 1:
+            hist_group = group
     for _, module in model.named_modules():
         if isinstance(module, TensorQuantizer) and not module._disabled:
             if module._use_constant_amax or module._constant_amax is not None:
@@ -53,12 +61,21 @@ def enable_stats_collection(model: nn.Module, arena_pool: AmaxArenaPool | None =
                 module.enable_calib()
                 if arena_pool is not None and isinstance(module._calibrator, MaxCalibrator):
                     module._calibrator.attach_arena(arena_pool)
+                if isinstance(module._calibrator, HistogramCalibrator) and module._calibrator._state is None:
+                    module._calibrator.dp_group = hist_group
             else:
                 module.disable()
 
 
 def finish_stats_collection(model: nn.Module, method: str | None = None, **kwargs):
-    """model_calib.py:1144-1167."""
+    """model_calib.py:1144-1167 (+ the data-parallel SUM of the histograms, when the calibrators collected as a group)."""
+    from .calib import HistogramCalibrator
+
+    groups = {id(c.dp_group): c.dp_group for c in
+              (getattr(m, "_calibrator", None) for m in model.modules() if isinstance(m, TensorQuantizer))
+              if isinstance(c, HistogramCalibrator) and c.dp_group is not False and c._state is not None}
+    for g in groups.values():
+        sync_histograms(model, g)
     for _, module in model.named_modules():
         if not isinstance(module, TensorQuantizer) or module._disabled:
             continue
@@ -84,6 +101,95 @@ def _dp_group(model):
     return None, True
 
 
+def _max_calibrators(model):
+    """(quantizer, MaxCalibrator) of every enabled quantizer that collects with a MaxCalibrator, in `named_modules` order
+    (identical on every rank of a data-parallel replica)."""
+    out = []
+    for m in model.modules():
+        if isinstance(m, TensorQuantizer) and not m._disabled and isinstance(getattr(m, "_calibrator", None), MaxCalibrator):
+            out.append((m, m._calibrator))
+    return out
+
+
+def _state_bits(cal):
+    """The int32 words holding a MaxCalibrator's running amax (arena slot or private tensor), or None before any collect."""
+    if cal._shape is None:
+        return None
+    return cal._slot_arena.bits(cal._slot) if cal._slot is not None else cal._bits
+
+
+def sync_max_calibrators(model, pool: AmaxArenaPool, group=None):
+    """The data-parallel exchange of the running amax of EVERY MaxCalibrator of `model` (reference: one
+    all_reduce(MAX) per quantizer, tensor_quantizer.py:1373-1385).  Fast path: ONE all-reduce over each arena of `pool` plus
+    ONE over the concatenated state of the calibrators that live outside it (they collected before this pool existed:
+    `enable_stats_collection` + `forward_loop` of the AWQ passes, a second `calibrate()` without `reset_amax`).  The fast path
+    needs the same arena layout on every rank; slots are created at a quantizer's first non-empty collect, so a rank that
+    never fed one (an empty MoE expert, an uneven forward_loop) has another layout: ranks first agree on a layout
+    signature and otherwise take the ordered per-quantizer exchange, which also hands the amax to the rank that saw no
+    data (the reference would hang in NCCL there).  Returns the set of calibrators whose state went through `pool`."""
+    cals = _max_calibrators(model)
+    arenas = pool.arenas()
+    in_pool = {id(c) for _, c in cals if c._slot is not None and any(c._slot_arena is a for a in arenas)}
+    strays = [c for _, c in cals if id(c) not in in_pool and _state_bits(c) is not None]
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return in_pool
+    dev = next((b.device for b in (_state_bits(c) for _, c in cals) if b is not None), None)
+    if dev is None:
+        dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+
+    def h(seq):
+        v = 1469598103934665603
+        for x in seq:
+            v = ((v ^ (int(x) & 0xFFFFFFFF)) * 1099511628211) & 0x7FFFFFFFFFFFFFF
+        return v
+
+    sig = torch.tensor([len(arenas), sum(a._used for a in arenas), h(x for a in arenas for s in a._slots for x in s),
+                        len(strays), h(_state_bits(c).numel() for c in strays),
+                        h(i for i, (_, c) in enumerate(cals) if id(c) in in_pool)], dtype=torch.int64, device=dev)
+    lo, hi = sig.clone(), sig.clone()
+    dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    if torch.equal(lo, hi):
+        pool.sync(group)
+        if strays:
+            flat = torch.cat([_state_bits(c).reshape(-1) for c in strays])
+            dist.all_reduce(flat, op=dist.ReduceOp.MAX, group=group)
+            off = 0
+            for c in strays:
+                b = _state_bits(c)
+                b.copy_(flat[off:off + b.numel()].view_as(b))
+                off += b.numel()
+                c._checked = False
+        return in_pool
+    # ---- layouts differ: ordered exchange, quantizer by quantizer in one flat buffer ----
+    sizes = torch.tensor([0 if _state_bits(c) is None else _state_bits(c).numel() for _, c in cals],
+                         dtype=torch.int64, device=dev)
+    agreed = sizes.clone()
+    dist.all_reduce(agreed, op=dist.ReduceOp.MAX, group=group)
+    agreed_l, sizes_l = agreed.tolist(), sizes.tolist()
+    flat = torch.zeros(sum(agreed_l), dtype=torch.int32, device=dev)
+    off = 0
+    for (_, c), n, mine in zip(cals, agreed_l, sizes_l):
+        if mine:
+            if mine != n:
+                raise RuntimeError("amax shape differs between data-parallel ranks")
+            flat[off:off + n] = _state_bits(c).reshape(-1)
+        off += n
+    dist.all_reduce(flat, op=dist.ReduceOp.MAX, group=group)
+    off = 0
+    for (q, c), n, mine in zip(cals, agreed_l, sizes_l):
+        if n and mine:
+            _state_bits(c).copy_(flat[off:off + n].view_as(_state_bits(c)))
+        elif n == 1:  # this rank never fed the quantizer: adopt the group's per-tensor amax
+            c._bits, c._slot, c._shape = flat[off:off + 1].clone(), None, ()
+            c._dtype = c._dtype or torch.float32
+        elif n:
+            warnings.warn("a per-channel quantizer saw no data on this rank; its amax stays unset here")
+        c._checked = False
+        off += n
+    return set()
+
+
 @torch.no_grad()
 def max_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, **_unused):
     """model_calib.py:310-498 (data-parallel sync only; TP / EP groups are outside this path)."""
@@ -93,19 +199,22 @@ def max_calibrate(model: nn.Module, forward_loop=None, distributed_sync=True, **
     if forward_loop is not None:
         forward_loop(model)
     # the one exchange: amax of every quantizer, all-reduce MAX over the data-parallel group
+    validated = {id(c) for _, c in _max_calibrators(model)
+                 if c._slot is not None and any(c._slot_arena is a for a in pool.arenas())}
     if distributed_sync and dist.is_available() and dist.is_initialized():
         group, ok = _dp_group(model)
         if ok:
-            pool.sync(group)
+            validated = sync_max_calibrators(model, pool, group)
     pool.check()  # one host read: AssertionError on NaN / inf like MaxCalibrator.collect (max.py:69-77)
-    for m in model.modules():
-        if isinstance(m, TensorQuantizer) and isinstance(getattr(m, "_calibrator", None), MaxCalibrator):
-            m._calibrator._checked = True
+    for _, c in _max_calibrators(model):
+        if id(c) in validated:
+            c._checked = True  # covered by pool.check(); every other calibrator validates itself in compute_amax()
     finish_stats_collection(model)
     if distributed_sync and dist.is_available() and dist.is_initialized():
-        # quantizers whose amax did not go through the arena — custom calibrators, and DISABLED quantizers that already
-        # hold an amax (AWQ's patched forwards calibrate the input quantizer per batch and leave it disabled): the
-        # reference's per-quantizer sync covers every quantizer with an ``_amax``, enabled or not (model_calib.py:117-130)
+        # quantizers whose amax did not come from a MaxCalibrator that was enabled here — custom calibrators, and DISABLED
+        # quantizers that already hold an amax (AWQ's patched forwards calibrate the input quantizer per batch and leave it
+        # disabled): the reference's per-quantizer sync covers every quantizer with an ``_amax``, enabled or not
+        # (model_calib.py:117-130)
         group, ok = _dp_group(model)
         for m in model.modules():
             if ok and isinstance(m, TensorQuantizer) and getattr(m, "_amax", None) is not None \
@@ -123,45 +232,47 @@ def _finalize_with_shared_state(model: nn.Module, weight_patterns=None):
 
 
 def sync_histograms(model: nn.Module, group=None):
-    """All-reduce-SUM of the histograms of every HistogramCalibrator over the data-parallel group.
+    """All-reduce(SUM) of the counts of every HistogramCalibrator over the data-parallel group, in ONE flat int64 buffer.
 
-    New behaviour (the reference does not synchronise histograms, calib/histogram.py:158-163).  Ranks first agree
-    on a common range (all-reduce MAX of the number of bins: every rank's bins have the width fixed by ITS first
-    batch, so the widths are exchanged too and must agree — they do when every rank saw the same first batch
-    statistics, otherwise this raises), then integer counts are summed exactly.  World size 1 is a no-op, i.e. the
-    reference's behaviour bit for bit."""
+    New behaviour (the reference does not synchronise histograms, calib/histogram.py:158-163).  The calibrators of a
+    data-parallel replica take identical range decisions batch by batch (`HistogramCalibrator.dp_group`: the batch
+    maximum is all-reduced(MAX) inside `collect`), so on every rank bin i means the same interval and the sum of the
+    ranks' exact integer counts is bit-identical to ONE process calibrating on the concatenation of the ranks' batches.
+    Ranks first verify that agreement (bin count, range, width of every calibrator: one MIN + one MAX exchange) and raise
+    if it does not hold - e.g. when the calibrators collected before `dp_group` was set.  World size 1 is a no-op, i.e.
+    the reference's behaviour bit for bit; a second call without a `collect` in between does nothing."""
     from .calib import HistogramCalibrator
 
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return
     cals = [m._calibrator for m in model.modules()
             if isinstance(m, TensorQuantizer) and isinstance(getattr(m, "_calibrator", None), HistogramCalibrator)
-            and m._calibrator._counts is not None]
+            and m._calibrator._state is not None and not m._calibrator._synced]
+    n_cals = torch.tensor([len(cals)], dtype=torch.int64, device=cals[0]._state.device if cals else None)
+    if cals:
+        lo, hi = n_cals.clone(), n_cals.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+        if int(lo) != int(hi):
+            raise RuntimeError("sync_histograms: ranks hold different numbers of histogram calibrators with data")
     if not cals:
         return
-    dev = cals[0]._counts.device
-    meta = torch.tensor([[c._counts.numel(), float(c._calib_bin_edges[1] - c._calib_bin_edges[0])] for c in cals],
-                        dtype=torch.float64, device=dev)
-    hi, lo = meta.clone(), meta.clone()
-    dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    dev = cals[0]._state.device
+    meta = torch.stack([c._state[:4] for c in cals]).to(torch.int64)  # bin count, range, width, last growth: all bit patterns
+    lo, hi = meta.clone(), meta.clone()
     dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
-    if not torch.equal(hi[:, 1], lo[:, 1]):
-        raise RuntimeError("sync_histograms: ranks disagree on the bin width (their first batches had different "
-                           "ranges); use HistogramCalibrator with an agreed initial range")
-    sizes = hi[:, 0].long().tolist()
-    flat = torch.zeros(sum(sizes), dtype=torch.int64, device=dev)
-    off = 0
-    for c, n in zip(cals, sizes):
-        flat[off:off + c._counts.numel()] = c._counts
-        off += n
+    dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
+    if not torch.equal(lo, hi):
+        raise RuntimeError("sync_histograms: ranks disagree on the bins of a histogram (bin count / range / width); "
+                           "calibrate with HistogramCalibrator.dp_group set from the first batch "
+                           "(enable_stats_collection does it) so that every rank takes the same range decisions")
+    sizes = [c._num_bins for c in cals]  # reads the state (and reports a frozen calibrator)
+    flat = torch.cat([c._buf[:n] for c, n in zip(cals, sizes)])
     dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
     off = 0
     for c, n in zip(cals, sizes):
-        if n != c._counts.numel():  # grow this rank's edges to the common range, same width
-            width = c._calib_bin_edges[1] - c._calib_bin_edges[0]
-            c._calib_bin_edges = torch.arange(0, n + 1, device=c._calib_bin_edges.device) * width
-            c._num_bins = n
-        c._counts = flat[off:off + n].clone()
+        c._buf[:n] = flat[off:off + n]
+        c._synced = True
         off += n
 
 
@@ -424,6 +535,7 @@ def _apply_weight_pre_quant_scale(linear, pre_quant_scale):
         return
     if mode is None:
         ops.scale_cols(w.data, s, out=w.data)
+        linear.invalidate_weight_cache()  # raw-pointer in-place write: the weight's version counter did not move
         _recalibrate_weight(linear)
         return
     bits = torch.zeros(w.shape[0] if mode == "row" else 1, dtype=torch.int32, device=w.device)
@@ -432,7 +544,7 @@ def _apply_weight_pre_quant_scale(linear, pre_quant_scale):
     amax = amax.view(-1, 1) if mode == "row" else amax.reshape(())
     q.reset_amax()
     q.amax = amax.to(w.dtype)
-    linear.__dict__.pop("_weight_collect_key", None)
+    linear.invalidate_weight_cache()  # raw-pointer in-place write above: the weight's version counter did not move
 
 
 @torch.no_grad()

@@ -52,12 +52,29 @@ def calibrate(model: nn.Module, algorithm: str | dict | None = "max", forward_lo
     model.eval()
     table[method](model, forward_loop=forward_loop, **kwargs)
     model.train(was_training)
-    # model_quant.py:119-122: warn on invalid amax after calibration
-    for name, module in model.named_modules():
-        if isinstance(module, TensorQuantizer):
-            for attr in ("_amax", "_pre_quant_scale"):
-                module.validate_attr(attr_name=attr, warn_error=True, name=name)
+    _validate_after_calibration(model)
     return model
+
+
+def _validate_after_calibration(model: nn.Module):
+    """model_quant.py:119-122: warn on negative / inf / NaN amax or pre_quant_scale after calibration.  The reference asks
+    each quantizer (three device->host reads per attribute: ~2700 syncs on a Llama-3-8B); here every attribute of a device
+    is checked by ONE reduction and one read, and only a failing model pays for the per-quantizer warnings."""
+    import torch
+
+    found = [(name, module, attr) for name, module in model.named_modules() if isinstance(module, TensorQuantizer)
+             for attr in ("_amax", "_pre_quant_scale")
+             if isinstance(getattr(module, attr, None), torch.Tensor) and not getattr(module, attr).is_meta]
+    by_dev: dict = {}
+    for item in found:
+        by_dev.setdefault(getattr(item[1], item[2]).device, []).append(item)
+    for items in by_dev.values():
+        flat = torch.cat([getattr(m, attr).detach().reshape(-1).float() for _, m, attr in items])
+        # >= 0 is False for NaN too; inf is the only bad value that passes it
+        if bool(torch.all((flat >= 0) & ~torch.isinf(flat))):
+            continue
+        for name, module, attr in items:
+            module.validate_attr(attr_name=attr, warn_error=True, name=name)
 
 
 def quantize(model: nn.Module, config: dict[str, Any], forward_loop: ForwardLoop | None = None) -> nn.Module:

@@ -77,6 +77,8 @@ class QuantModule(nn.Module):
                     and getattr(q, "is_enabled", True):
                 with torch.no_grad():
                     weight.data.copy_(q(weight.float().contiguous()).to(weight.dtype))
+                if hasattr(self, "invalidate_weight_cache"):
+                    self.invalidate_weight_cache()  # `.data.copy_` does not move the weight's version counter
                 q.disable()
                 if not keep_attrs:
                     for name in ("_pre_quant_scale", "_amax"):
@@ -112,6 +114,44 @@ class QuantInputBase(QuantModule):
         return self.output_quantizer(output)
 
 
+_WEIGHT_CACHES = ("_wq_cache", "_w4_cache", "_w8_cache", "_weight_collect_key")
+CHECK_CACHE = __import__("os").environ.get("MODELOPT_B200_CHECK_CACHE", "0") not in ("", "0")
+
+
+def _no_cache() -> bool:
+    from .. import ops
+
+    return ops.NO_CACHE
+
+
+def _fingerprint(w):
+    """Debug aid (MODELOPT_B200_CHECK_CACHE=1): content checksum of a weight, to catch a write through `.data` / a raw
+    pointer that left (data_ptr, _version) unchanged and would otherwise be served a stale fake-quantized weight."""
+    f = w.detach().float()
+    return torch.stack([f.sum(), f.abs().sum(), f.reshape(-1)[:: max(1, f.numel() // 997)].sum()]).tolist()
+
+
+def _cache_lookup(module, slot, key, w):
+    """Cached value of `slot` for `key`, or None.  With MODELOPT_B200_NO_CACHE=1 nothing is ever served from a cache (the
+    reference's always-requantize behaviour); with MODELOPT_B200_CHECK_CACHE=1 a hit is verified against a checksum."""
+    if _no_cache():
+        return None
+    hit = module.__dict__.get(slot)
+    if hit is None or hit[0] != key:
+        return None
+    if CHECK_CACHE and len(hit) > 2 and hit[2] != _fingerprint(w):
+        raise RuntimeError(
+            f"modelopt_b200: the weight of {type(module).__name__} changed without its version counter moving (a write "
+            "through `.data` or a raw pointer); call module.invalidate_weight_cache() after such writes or set "
+            "MODELOPT_B200_NO_CACHE=1")
+    return hit[1]
+
+
+def _cache_store(module, slot, key, value, w):
+    if not _no_cache():
+        module.__dict__[slot] = (key, value, _fingerprint(w)) if CHECK_CACHE else (key, value)
+
+
 def _weight_get(self):
     w = self._parameters["weight"] if "weight" in self._parameters else self._buffers.get("weight")
     if w is None or not self.__dict__.get("_enable_weight_quantization", False):
@@ -120,7 +160,7 @@ def _weight_get(self):
     if (isinstance(q, TensorQuantizer) and q._if_calib and not q._if_quant and not q._disabled
             and isinstance(q._calibrator, MaxCalibrator) and q.pre_quant_scale is None):
         key = (w.data_ptr(), w._version, tuple(w.shape))
-        if self.__dict__.get("_weight_collect_key") == key and q._calibrator._shape is not None:
+        if not _no_cache() and self.__dict__.get("_weight_collect_key") == key and q._calibrator._shape is not None:
             return w  # already folded into the running amax; max is idempotent
         self.__dict__["_weight_collect_key"] = key
     return q(w)
@@ -145,6 +185,16 @@ class QuantLinearConvBase(QuantInputBase):
         super()._setup()
         self.weight_quantizer = TensorQuantizer(self.default_quant_desc_weight)
         self.__dict__["_enable_weight_quantization"] = False
+
+    def invalidate_weight_cache(self):
+        """Drop every cached function of the weight (fake-quantized weight, packed NVFP4 / FP8 operands, the "already
+        collected" mark) and the quantizers' fp32 amax copies.  The caches key on (data_ptr, _version) of the weight and
+        of the quantizer buffers; call this after writing through `.data` or a raw pointer, which moves neither."""
+        for k in _WEIGHT_CACHES:
+            self.__dict__.pop(k, None)
+        for q in self.modules():
+            if isinstance(q, TensorQuantizer):
+                q.__dict__.pop("_amax_f32", None)
 
     @contextlib.contextmanager
     def quantize_weight(self):
@@ -216,12 +266,12 @@ class _QuantLinear(QuantLinearConvBase):
             with self.quantize_weight():
                 return self.weight
         key = (w.data_ptr(), w._version, tuple(w.shape), w.dtype, qk)
-        hit = self.__dict__.get("_wq_cache")
-        if hit is not None and hit[0] == key:
-            return hit[1]
+        hit = _cache_lookup(self, "_wq_cache", key, w)
+        if hit is not None:
+            return hit
         with torch.no_grad():
             wq = q(w)
-        self.__dict__["_wq_cache"] = (key, wq)
+        _cache_store(self, "_wq_cache", key, wq, w)
         return wq
 
     # ---- opt-in: real-quant GEMMs (FP8 per-tensor, NVFP4 W4A4) on the tensor-core paths, not the bf16 simulation ----
@@ -260,12 +310,12 @@ class _QuantLinear(QuantLinearConvBase):
         w = self._parameters["weight"]
         q = self.weight_quantizer
         key = (w.data_ptr(), w._version, tuple(w.shape), w.dtype, q.cache_key())
-        hit = self.__dict__.get("_w4_cache")
-        if hit is not None and hit[0] == key:
-            return hit[1]
+        hit = _cache_lookup(self, "_w4_cache", key, w)
+        if hit is not None:
+            return hit
         with torch.no_grad():
             packed = ops.nvfp4_quantize_operand(w.detach(), q._amax.float().amax(), 256)
-        self.__dict__["_w4_cache"] = (key, packed)
+        _cache_store(self, "_w4_cache", key, packed, w)
         return packed
 
     def _forward_real_quant(self, input):
@@ -303,13 +353,13 @@ class _QuantLinear(QuantLinearConvBase):
         w = self._parameters["weight"]
         q = self.weight_quantizer
         key = (w.data_ptr(), w._version, tuple(w.shape), w.dtype, q.cache_key())
-        hit = self.__dict__.get("_w8_cache")
-        if hit is not None and hit[0] == key:
-            return hit[1]
+        hit = _cache_lookup(self, "_w8_cache", key, w)
+        if hit is not None:
+            return hit
         with torch.no_grad():
             scale_b = ops.div_scalar(q._amax.float().reshape(1), 448.0)
             packed = (ops.q8_pack(w.detach(), scale_b, "fp8_sat"), scale_b)
-        self.__dict__["_w8_cache"] = (key, packed)
+        _cache_store(self, "_w8_cache", key, packed, w)
         return packed
 
     def forward(self, input, *args, **kwargs):

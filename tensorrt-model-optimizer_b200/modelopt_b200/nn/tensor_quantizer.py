@@ -24,7 +24,9 @@ from torch import nn
 
 from .. import calib
 from ..config import QuantizerAttributeConfig
-from ..tensor_quant import (dynamic_block_quant, fake_tensor_quant, scaled_e4m3, static_blockwise_fp4_fake_quant)
+from ..tensor_quant import (DynamicBlockQuantizationFunction, FakeTensorQuantFunction, ScaledE4M3Function,
+                            call_functional, dynamic_block_quant, fake_tensor_quant, scaled_e4m3,
+                            static_blockwise_fp4_fake_quant)
 from .. import ops
 from ..utils import convert_quantization_axis_to_reduce_axis, reduce_amax
 
@@ -77,7 +79,7 @@ class TensorQuantizer(nn.Module):
     """Quantizes (fake or real) or calibrates its input, depending on ``_if_quant`` / ``_if_calib``."""
 
     _skip_properties_for_save_restore = {"_calibrator", "_bias_calibrator", "_original_shape", "_block_reshape_size",
-                                         "_padding", "_quantizer_cache", "_slices"}
+                                         "_padding", "_quantizer_cache", "_slices", "_amax_f32"}
 
     def __init__(self, quant_attribute_cfg=None, if_quant=True, if_calib=False, amax=None):
         super().__init__()
@@ -149,7 +151,9 @@ class TensorQuantizer(nn.Module):
             assert attribute in QuantizerAttributeConfig.model_fields, (
                 f"{attribute} is not a valid `TensorQuantizer` attribute")
             name, setter = custom.get(attribute, (f"_{attribute}", lambda v: v))
-            setattr(self, name, setter(val))
+            # plain Python values (never a Parameter / Module / buffer): skip nn.Module.__setattr__'s type checks, which
+            # dominate quantizer construction and set_quantizer_by_cfg on a 676-quantizer model (properties still apply)
+            object.__setattr__(self, name, setter(val))
         if self.is_mx_format:
             self._pass_through_bwd = True  # tensor_quantizer.py:289-290
 
@@ -410,6 +414,16 @@ class TensorQuantizer(nn.Module):
             return torch.tensor(torch.finfo(torch.float8_e4m3fn).max, device=inputs.device)
         if hasattr(self, "_amax"):
             amax = self._amax
+            if amax.dtype != torch.float32 and amax.is_cuda and not ops.NO_CACHE:
+                # the kernels take fp32 amax (tensor_quant_gpu.cu:83 `amax.to(float)`): keep the converted copy while the
+                # buffer's (address, version counter) is unchanged instead of launching a cast kernel per forward
+                key = (amax.data_ptr(), amax._version, inputs.device)
+                hit = self.__dict__.get("_amax_f32")
+                if hit is not None and hit[0] == key:
+                    return hit[1]
+                f32 = amax.detach().to(device=inputs.device, dtype=torch.float32)
+                self.__dict__["_amax_f32"] = (key, f32)
+                return f32
             if amax.device != inputs.device:
                 amax = amax.to(inputs.device)
         else:
@@ -429,16 +443,17 @@ class TensorQuantizer(nn.Module):
             block_size = bs.get(-1, None) or bs.get(inputs.dim() - 1, None)
             if block_size is None:
                 raise ValueError("block size for dynamic quantization not found.")
-            return dynamic_block_quant(inputs, block_size, amax, None, self._num_bits, bs.get("scale_bits", None),
-                                       getattr(self, "_trt_high_precision_dtype", None),
-                                       getattr(self, "_onnx_quantizer_type", None), self._pass_through_bwd)
+            return call_functional(DynamicBlockQuantizationFunction, inputs, block_size, amax, None, self._num_bits,
+                                   bs.get("scale_bits", None), getattr(self, "_trt_high_precision_dtype", None),
+                                   getattr(self, "_onnx_quantizer_type", None), self._pass_through_bwd)
         if isinstance(self._num_bits, tuple):
             E, M = self._num_bits  # noqa: N806
-            return scaled_e4m3(inputs, amax, None, E, M, self._trt_high_precision_dtype, self._pass_through_bwd)
-        return fake_tensor_quant(inputs, amax, None, self._num_bits, self._unsigned, self._narrow_range,
-                                 self._trt_high_precision_dtype, self._pass_through_bwd,
-                                 bs.get(-1) if bs else None,
-                                 self.axis[0] if isinstance(self.axis, tuple) else self.axis)
+            return call_functional(ScaledE4M3Function, inputs, amax, None, E, M, self._trt_high_precision_dtype,
+                                   self._pass_through_bwd)
+        return call_functional(FakeTensorQuantFunction, inputs, amax, None, self._num_bits, self._unsigned,
+                               self._narrow_range, self._trt_high_precision_dtype, self._pass_through_bwd,
+                               bs.get(-1) if bs else None,
+                               self.axis[0] if isinstance(self.axis, tuple) else self.axis)
 
     def _is_real_quantize_support(self):
         """tensor_quantizer.py:785-794."""

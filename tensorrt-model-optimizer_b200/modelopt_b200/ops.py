@@ -81,7 +81,14 @@ def _cuda(t: torch.Tensor, what: str):
         )
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def _stream(t: torch.Tensor) -> int:
+    """cudaStream_t of torch's current stream on t's device (the raw-handle query is ~10 us cheaper per call than building
+    a torch.cuda.Stream object)."""
+    if _raw_stream is not None and t.device.index is not None:
+        return _raw_stream(t.device.index)
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
@@ -101,6 +108,13 @@ class _dev:
     def __exit__(self, *a):
         if self.prev is not None:
             torch.cuda.set_device(self.prev)
+
+
+# MODELOPT_B200_NO_CACHE=1 turns off every cache that is keyed on a tensor's (address, version counter): the quantizer's
+# fp32 amax copy and the modules' fake-quantized / packed weight caches.  A write through `.data` or a raw pointer does
+# not move the version counter, so code that mutates amax or weights that way needs this switch (or
+# `invalidate_weight_cache()`); the reference re-quantizes on every forward.
+NO_CACHE = os.environ.get("MODELOPT_B200_NO_CACHE", "0") not in ("", "0")
 
 
 def _f32_vec(a: torch.Tensor, like: torch.Tensor) -> torch.Tensor:
@@ -452,6 +466,29 @@ def hist_into(x, range_max, counts, amax_bits=None, skip_zeros=False):
         _launched(_lib.load().mo_hist(x.data_ptr(), x.numel(), _code(x), range_max.data_ptr(), counts.numel(),
                                       counts.data_ptr(), amax_bits.data_ptr() if amax_bits is not None else None,
                                       int(bool(skip_zeros)), _stream(x)), "mo_hist")
+
+
+def hist_collect_begin(x, state, counts, smem_bins_hint, skip_zeros, first):
+    """First half of a sync-free HistogramCalibrator.collect (mo_hist_collect_begin): first batch = max|x| into
+    state[MO_HIST_BATCH_AMAX]; later batches = bin |x| under the state's current range and fold max|x| in the same read."""
+    _cuda(x, "hist_collect_begin")
+    assert state.dtype == torch.int32 and state.numel() >= 16 and state.device == x.device
+    assert counts.dtype == torch.int64 and counts.is_contiguous() and counts.device == x.device and x.is_contiguous()
+    with _dev(x):
+        _launched(_lib.load().mo_hist_collect_begin(x.data_ptr(), x.numel(), _code(x), state.data_ptr(), counts.data_ptr(),
+                                                    counts.numel(), int(smem_bins_hint), int(bool(skip_zeros)),
+                                                    int(bool(first)), _stream(x)), "mo_hist_collect_begin")
+
+
+def hist_collect_end(x, state, counts, smem_bins_hint, skip_zeros, first, init_bins, numerics=None):
+    """Second half (mo_hist_collect_end): first batch = fix the range and bin; later batches = the reference's range-growth
+    decision on the device, plus the undo / redo passes, which return at once unless the range grew."""
+    _cuda(x, "hist_collect_end")
+    with _dev(x):
+        _launched(_lib.load().mo_hist_collect_end(x.data_ptr(), x.numel(), _code(x), state.data_ptr(), counts.data_ptr(),
+                                                  counts.numel(), int(smem_bins_hint), int(bool(skip_zeros)),
+                                                  int(bool(first)), int(init_bins), _mode(numerics), _stream(x)),
+                  "mo_hist_collect_end", n=2 if first else 3)
 
 
 def hist_percentile_index(counts, percentile: float) -> torch.Tensor:
@@ -1031,6 +1068,12 @@ def linear_supported(x, weight, bias=None) -> bool:
     N, K = weight.shape
     if K < 8 or K % 8 or N % 8 or (bias is not None and (bias.dtype != x.dtype or bias.numel() != N)):
         return False
+    # TMA descriptors and the 16-byte epilogue accesses need 16-byte aligned bases: a contiguous view with an odd storage
+    # offset (flat-parameter slices) takes the caller's eager path instead of failing with MO_ERR_ARG.  A non-contiguous
+    # operand is copied by .contiguous() in the wrappers, and fresh allocations are aligned.
+    for t in (x, weight, bias):
+        if t is not None and t.is_contiguous() and t.data_ptr() % 16:
+            return False
     return True
 
 

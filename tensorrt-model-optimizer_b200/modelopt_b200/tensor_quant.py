@@ -266,6 +266,27 @@ class IntCastSTEFunction(Function):
         return torch.where(inside, grad_outputs, torch.zeros_like(grad_outputs)), None, None, None
 
 
+class _NoGradCtx:
+    """Stand-in for the autograd context when no gradient can flow: `Function.forward(_NOCTX, ...)` runs the same code
+    as `.apply` without building a graph node (about 15 us of host time per quantizer call)."""
+
+    needs_input_grad = ()
+
+    @staticmethod
+    def save_for_backward(*tensors):
+        pass
+
+
+_NOCTX = _NoGradCtx()
+
+
+def call_functional(fn_cls, inputs, *args):
+    """`fn_cls.apply(inputs, *args)`; bypasses autograd when grad mode is off or the input does not require grad."""
+    if torch.is_grad_enabled() and isinstance(inputs, torch.Tensor) and inputs.requires_grad:
+        return fn_cls.apply(inputs, *args)
+    return fn_cls.forward(_NOCTX, inputs, *args)
+
+
 fake_tensor_quant = FakeTensorQuantFunction.apply
 int_cast_ste = IntCastSTEFunction.apply
 scaled_e4m3 = ScaledE4M3Function.apply

@@ -111,30 +111,48 @@ def _disabled_amax_sync(rank, world):
 
 
 def _hist_sync(rank, world):
+    """sync_histograms: ranks that took the same range decisions (what the per-batch all-reduce(MAX) of the batch maximum
+    inside collect guarantees) sum their exact counts in one flat buffer; ranks that did not are refused.  The device
+    state is written by hand here (the kernels need a GPU)."""
     import modelopt_b200 as mtq
     from modelopt_b200.calib import HistogramCalibrator
     from torch import nn
 
-    m = nn.Sequential(nn.Linear(8, 8))
+    m = nn.Sequential(nn.Linear(8, 8), nn.Linear(8, 8))
     mtq.replace_quant_module(m)
     mtq.set_quantizer_by_cfg(m, [{"quantizer_name": "*", "enable": False},
                                  {"quantizer_name": "*input_quantizer", "cfg": {"num_bits": 8, "calibrator": "histogram"}}])
-    cal = m[0].input_quantizer._calibrator
-    assert isinstance(cal, HistogramCalibrator)
-    nb = 2048 if rank == 0 else 2500  # rank 1's range grew
-    cal._counts = torch.arange(nb, dtype=torch.int64) % 7 + rank
-    cal._calib_bin_edges = torch.arange(0, nb + 1, dtype=torch.float32) * 0.5
-    cal._num_bins = nb
-    mine = cal._counts.clone()
+    mtq.enable_stats_collection(m)
+    cals = [m[0].input_quantizer._calibrator, m[1].input_quantizer._calibrator]
+    assert all(isinstance(c, HistogramCalibrator) and c.dp_group is None for c in cals)  # the default (world) group
+
+    def f32_bits(v):
+        return int(torch.tensor([v], dtype=torch.float32).view(torch.int32)[0])
+
+    mine = []
+    for k, (cal, nb) in enumerate(zip(cals, (2048, 2500))):
+        cal._state = torch.zeros(16, dtype=torch.int32)
+        cal._state[0], cal._state[1], cal._state[2] = nb, f32_bits(nb * 0.5), f32_bits(0.5)
+        cal._state[3] = 0 if nb == 2048 else f32_bits(nb * 0.5 + 0.25)
+        cal._state[5] = f32_bits(1024.0)
+        cal._buf = torch.zeros(4096, dtype=torch.int64)
+        cal._buf[:nb] = torch.arange(nb, dtype=torch.int64) % (7 + k) + rank
+        mine.append(cal._buf[:nb].clone())
     mtq.sync_histograms(m)
-    assert cal._counts.numel() == 2500 and cal._calib_bin_edges.numel() == 2501
-    other_nb = 2500 if rank == 0 else 2048
-    other = torch.arange(other_nb, dtype=torch.int64) % 7 + (1 - rank)
-    want = torch.zeros(2500, dtype=torch.int64)
-    want[:nb] += mine
-    want[:other_nb] += other
-    assert torch.equal(cal._counts, want)
-    assert float(cal._calib_bin_edges[-1]) == 1250.0
+    for k, (cal, nb) in enumerate(zip(cals, (2048, 2500))):
+        want = sum(torch.arange(nb, dtype=torch.int64) % (7 + k) + r for r in range(world))
+        assert cal._synced and torch.equal(cal._counts, want)
+        assert cal._calib_bin_edges.numel() == nb + 1
+    before = [c._counts.clone() for c in cals]
+    mtq.sync_histograms(m)  # already summed: a second call must not sum again
+    assert all(torch.equal(a, c._counts) for a, c in zip(before, cals))
+    # ranks whose ranges diverged (no per-batch exchange): refused, not silently mis-added
+    for cal in cals:
+        cal._synced = False
+    cals[1]._state[0] = 2500 + rank
+    cals[1]._snap_valid = False
+    with pytest.raises(RuntimeError, match="disagree"):
+        mtq.sync_histograms(m)
 
 
 def _hessian_sync(rank, world):
@@ -161,6 +179,81 @@ def _hessian_sync(rank, world):
     assert all(torch.equal(t, gathered[0]) for t in gathered)  # bit-identical on every rank
 
 
-@pytest.mark.parametrize("fn", ["_arena_sync", "_quantize_sync", "_hist_sync", "_hessian_sync", "_disabled_amax_sync"])
+def _calibrating_model():
+    import modelopt_b200 as mtq
+    from modelopt_b200.arena import AmaxArenaPool
+    from torch import nn
+
+    m = nn.Sequential(nn.Linear(8, 8), nn.Linear(8, 4))
+    mtq.replace_quant_module(m)
+    mtq.set_quantizer_by_cfg(m, mtq.FP8_DEFAULT_CFG["quant_cfg"])  # per-tensor everywhere: 4 scalar amax
+    pool = AmaxArenaPool()
+    mtq.enable_stats_collection(m, pool)
+    qs = [q for q in m.modules() if isinstance(q, mtq.TensorQuantizer) and q._if_calib]
+    assert len(qs) == 4
+    return m, pool, qs
+
+
+def _put(cal, arena, value):
+    """What MaxCalibrator.collect leaves behind: a scalar running amax in `arena` (or private when arena is None)."""
+    if arena is None:
+        cal._bits = torch.tensor([value], dtype=torch.float32).view(torch.int32)
+    else:
+        cal._slot, cal._slot_arena = arena.alloc(1), arena
+        arena.amax(cal._slot)[:] = value
+    cal._shape, cal._dtype = (), torch.float32
+
+
+def _stray_calibrators_sync(rank, world):
+    """Calibrators whose state lives OUTSIDE this call's pool (they collected before it existed: AWQ's stats passes, a second
+    calibrate() without reset_amax) still take part in the exchange, and only pool-backed ones count as pool-validated."""
+    from modelopt_b200.arena import AmaxArena
+    from modelopt_b200.model_calib import max_calibrate, sync_max_calibrators
+
+    m, pool, qs = _calibrating_model()
+    old = AmaxArena("cpu")
+    _put(qs[0]._calibrator, pool.get("cpu"), 1.0 + rank)
+    _put(qs[1]._calibrator, None, 2.0 + 2 * rank)       # private bits
+    _put(qs[2]._calibrator, old, 3.0 - rank)            # an older call's arena
+    _put(qs[3]._calibrator, pool.get("cpu"), 4.0 + rank)
+    validated = sync_max_calibrators(m, pool, None)
+    assert validated == {id(qs[0]._calibrator), id(qs[3]._calibrator)}
+    got = [float(q._calibrator._calib_amax) for q in qs]
+    assert got == [1.0 + world - 1, 2.0 + 2 * (world - 1), 3.0, 4.0 + world - 1], got
+    # the whole flow: a second max_calibrate (fresh pool) on calibrators that keep their old state
+    for i, q in enumerate(qs):
+        b = q._calibrator._slot_arena.bits(q._calibrator._slot) if q._calibrator._slot is not None else q._calibrator._bits
+        b.view(torch.float32)[:] = 10.0 * (i + 1) + rank
+    for mod in m:
+        mod.__dict__["_weight_collect_key"] = None
+    import modelopt_b200.model_calib as mc
+
+    orig = mc.weight_only_quantize
+    mc.weight_only_quantize = lambda model: None  # no kernels on the CPU box
+    try:
+        max_calibrate(m, lambda mod: None, distributed_sync=True)
+    finally:
+        mc.weight_only_quantize = orig
+    assert [float(q.amax) for q in qs] == [10.0 * (i + 1) + world - 1 for i in range(4)]
+
+
+def _uneven_layout_sync(rank, world):
+    """One rank never fed a quantizer (empty MoE expert, uneven forward_loop): the arena layouts differ, the ranks notice
+    and exchange quantizer by quantizer; the rank without data adopts the group's amax instead of hanging in the collective."""
+    from modelopt_b200.model_calib import sync_max_calibrators
+
+    m, pool, qs = _calibrating_model()
+    arena = pool.get("cpu")
+    for i, q in enumerate(qs):
+        if rank == 1 and i == 1:
+            continue  # no data on this rank
+        _put(q._calibrator, arena, (i + 1) * (1.0 + rank))
+    sync_max_calibrators(m, pool, None)
+    got = [float(q._calibrator._calib_amax) for q in qs]
+    assert got == [1.0 * world, 2.0, 3.0 * world, 4.0 * world], got
+
+
+@pytest.mark.parametrize("fn", ["_arena_sync", "_quantize_sync", "_hist_sync", "_hessian_sync", "_disabled_amax_sync",
+                                "_stray_calibrators_sync", "_uneven_layout_sync"])
 def test_world_size_2(fn):
     _spawn(fn)

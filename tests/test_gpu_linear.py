@@ -188,3 +188,70 @@ def test_cta_pair_kernel_equals_single_cta(dt, M, N, K):
     assert abs(l1.item() - l2.item()) <= 1e-12 * max(1.0, abs(l1.item()))  # fp64 atomics: order only
     want = (x.float() @ w.float().t() + b.float())
     assert (two.float() - want).abs().max() <= 2.0 ** -7 * want.abs().max() + 1e-6
+
+
+def test_unaligned_views_fall_back_to_the_eager_linear():
+    """A contiguous weight / input view whose storage offset is not 16-byte aligned (flat-parameter slices) is not
+    offered to the tcgen05 kernels (`linear_supported` is False) and the module forward still works."""
+    import modelopt_b200 as mtq
+    from modelopt_b200 import config as qcfg
+    from modelopt_b200 import ops
+
+    torch.manual_seed(0)
+    flat = (torch.randn(64 * 128 + 3, device="cuda") * 0.05).to(torch.bfloat16)
+    w = flat[3:].view(64, 128)                      # 6-byte offset
+    x = torch.randn(32, 128, device="cuda", dtype=torch.bfloat16)
+    assert w.is_contiguous() and w.data_ptr() % 16 != 0
+    assert not ops.linear_supported(x, w)
+    assert ops.linear_supported(x, w.clone())
+    lin = torch.nn.Linear(128, 64, bias=False, device="cuda", dtype=torch.bfloat16)
+    lin.weight = torch.nn.Parameter(w)
+    m = torch.nn.Sequential(lin)
+    mtq.quantize(m, qcfg.FP8_DEFAULT_CFG, lambda mod: mod(x))
+    with torch.no_grad():
+        y = m(x)
+    ref = torch.nn.Linear(128, 64, bias=False, device="cuda", dtype=torch.bfloat16)
+    ref.weight = torch.nn.Parameter(w.clone())
+    m2 = torch.nn.Sequential(ref)
+    mtq.quantize(m2, qcfg.FP8_DEFAULT_CFG, lambda mod: mod(x))
+    with torch.no_grad():
+        y2 = m2(x)
+    assert (y.float() - y2.float()).abs().max().item() <= 2.0 ** -7 * y2.float().abs().max().item()
+
+
+def test_weight_cache_invalidation_and_opt_out():
+    """A write through `.data` leaves (data_ptr, _version) unchanged: the cached fake-quantized weight is stale until
+    `invalidate_weight_cache()`; MODELOPT_B200_NO_CACHE (ops.NO_CACHE) restores the reference's always-requantize
+    behaviour, and the debug checksum (quant_module.CHECK_CACHE) turns the stale hit into an error."""
+    from modelopt_b200 import ops
+    from modelopt_b200.nn import quant_module as qm
+
+    m, data = _quant_linear("FP8_DEFAULT_CFG")
+    x = data[0]
+    lin = m[0]
+    with torch.no_grad():
+        y0 = m(x)
+        lin.weight_quantizer.reset_amax()  # dynamic amax: the fake-quantized weight follows the weight
+        y0 = m(x)
+        lin._parameters["weight"].data.mul_(2.0)          # no version bump
+        stale = m(x)
+        lin.invalidate_weight_cache()
+        fresh = m(x)
+        assert not torch.equal(stale, fresh)
+        lin._parameters["weight"].data.mul_(0.5)
+        old = ops.NO_CACHE
+        ops.NO_CACHE = True
+        try:
+            assert torch.equal(m(x), y0)                  # no cache: the `.data` write is seen at once
+        finally:
+            ops.NO_CACHE = old
+        lin.invalidate_weight_cache()
+        qm.CHECK_CACHE = True
+        try:
+            m(x)                                          # fills the cache with a checksum
+            lin._parameters["weight"].data.mul_(2.0)
+            with pytest.raises(RuntimeError, match="version counter"):
+                m(x)
+        finally:
+            qm.CHECK_CACHE = False
+            lin.invalidate_weight_cache()

@@ -89,6 +89,59 @@ def main():
             if rank == 0:
                 print(f"{preset:38s} {k:34s} ranks identical: {same_ranks}"
                       f"{'' if same_ranks or not must else '   <-- FAIL'}{'' if must else '   (reported only)'}", flush=True)
+    # histogram calibration (HistogramCalibrator + entropy / percentile / mse searches): every rank feeds its own batches,
+    # several of which grow the range; the batch maximum is all-reduced inside collect, the counts are summed at finish.
+    # Must equal - bit for bit - ONE rank calibrating on the rank-concatenated batches with no sync at all.
+    from modelopt_b200 import model_calib
+    from modelopt_b200.calib import HistogramCalibrator
+
+    hist_cfg = [{"quantizer_name": "*", "enable": False},
+                {"quantizer_name": "*input_quantizer", "cfg": {"num_bits": 8, "calibrator": "histogram"}}]
+    gh = torch.Generator(device="cuda").manual_seed(11)
+    steps = 5
+    hb = [[(torch.randn(128, 512, device="cuda", generator=gh) * (0.5 + 0.9 * s + 0.35 * r)).to(torch.bfloat16)
+           for r in range(world)] for s in range(steps)]  # hb[step][rank]; later steps and higher ranks reach further out
+
+    def hist_run(model, feed, sync):
+        mtq.replace_quant_module(model)
+        mtq.set_quantizer_by_cfg(model, hist_cfg)
+        model_calib.enable_stats_collection(model, distributed_sync=sync)
+        with torch.no_grad():
+            for b in feed:
+                model(b)
+        cals = {n: q._calibrator for n, q in model.named_modules()
+                if isinstance(q, TensorQuantizer) and isinstance(getattr(q, "_calibrator", None), HistogramCalibrator)
+                and q._calibrator._state is not None}
+        res = {}
+        if sync:
+            model_calib.sync_histograms(model)
+        for n, c in cals.items():
+            res[n + ".counts"] = c._counts.clone()
+            res[n + ".edges"] = c._calib_bin_edges.to("cuda").float().clone()
+            for method, kw in (("entropy", {}), ("percentile", {"percentile": 99.9}), ("mse", {})):
+                import warnings as _w
+                with _w.catch_warnings():
+                    _w.simplefilter("ignore")
+                    res[f"{n}.{method}"] = c.compute_amax(method, **kw).float().reshape(1).cuda()
+        return res
+
+    mine = hist_run(copy.deepcopy(base), [hb[s][rank] for s in range(steps)], True)
+    truth = hist_run(copy.deepcopy(base), [torch.cat(hb[s]) for s in range(steps)], False)
+    assert mine.keys() == truth.keys() and len(mine) == 10, sorted(mine)
+    grew = int(truth["0.input_quantizer.counts"].numel()) > 2048
+    ok &= grew
+    for k, v in mine.items():
+        same_shape = v.shape == truth[k].shape
+        gathered = [torch.empty_like(v) for _ in range(world)]
+        dist.all_gather(gathered, v.contiguous())
+        same_ranks = all(torch.equal(x, gathered[0]) for x in gathered)
+        exact = same_shape and torch.equal(v, truth[k])
+        ok &= same_ranks and exact
+        if rank == 0:
+            print(f"{'histogram (entropy/percentile/mse)':38s} {k:34s} ranks identical: {same_ranks}  == single-rank on "
+                  f"concatenated batches: {exact} ({v.numel()} values){'' if same_ranks and exact else '   <-- FAIL'}", flush=True)
+    if rank == 0:
+        print(f"{'histogram':38s} range grew during calibration: {grew} ({truth['0.input_quantizer.counts'].numel()} bins)", flush=True)
     # control: without the Hessian sync the ranks refine to different weight amaxes (what the reference warns about)
     import warnings
     c0 = copy.deepcopy(qcfg.NVFP4_W4A4_WEIGHT_LOCAL_HESSIAN_CFG)
