@@ -147,9 +147,71 @@ def _cache_lookup(module, slot, key, w):
     return hit[1]
 
 
+# Device memory the cached functions of the weights (fake-quantized copies, packed operands) may take in total, per
+# device.  A cached fake-quantized weight doubles that weight's footprint: fine for an 8B model (14 GB), impossible for a
+# 70B replica on one 180 GB GPU, where the weights past the budget are re-quantized on every forward like the reference
+# does (quant_module.py:192-278).  MODELOPT_B200_WEIGHT_CACHE_GB overrides (0 = never cache).
+_CACHE_BUDGET_GB = __import__("os").environ.get("MODELOPT_B200_WEIGHT_CACHE_GB")
+_CACHE_USED: dict = {}
+
+
+def _cache_budget(device) -> int:
+    if _CACHE_BUDGET_GB is not None:
+        return int(float(_CACHE_BUDGET_GB) * (1 << 30))
+    total = torch.cuda.get_device_properties(device).total_memory
+    return min(32 << 30, total // 5)
+
+
+def _nbytes(value) -> int:
+    if isinstance(value, torch.Tensor):
+        return value.numel() * value.element_size()
+    if isinstance(value, (tuple, list)):
+        return sum(_nbytes(v) for v in value)
+    return 0
+
+
+def _first_tensor(value):
+    if isinstance(value, torch.Tensor):
+        return value
+    if isinstance(value, (tuple, list)):
+        for v in value:
+            t = _first_tensor(v)
+            if t is not None:
+                return t
+    return None
+
+
+def _release(dev, n):
+    _CACHE_USED[dev] = _CACHE_USED.get(dev, 0) - n
+
+
+def _cache_drop(module, slot):
+    module.__dict__.pop(slot, None)  # the budget is returned when the cached tensor dies (weakref.finalize below)
+
+
 def _cache_store(module, slot, key, value, w):
-    if not _no_cache():
-        module.__dict__[slot] = (key, value, _fingerprint(w)) if CHECK_CACHE else (key, value)
+    if _no_cache():
+        return
+    import weakref
+
+    _cache_drop(module, slot)
+    n, dev = _nbytes(value), w.device
+    t = _first_tensor(value)
+    if t is not None and t.data_ptr() == w.data_ptr():
+        n = 0  # a disabled quantizer returns the weight itself: nothing extra is held
+    if w.is_cuda and n:
+        if _CACHE_USED.get(dev, 0) + n > _cache_budget(dev):
+            return  # over the budget: this weight is re-quantized per forward
+        if _CACHE_BUDGET_GB is None:
+            # and never into the last 15 % of the device (a 70B replica leaves ~37 GB of a B200: activations need most of it)
+            free, total = torch.cuda.mem_get_info(dev)
+            free += torch.cuda.memory_reserved(dev) - torch.cuda.memory_allocated(dev)
+            if free - n < 0.15 * total:
+                return
+    if t is not None and n:
+        _CACHE_USED[dev] = _CACHE_USED.get(dev, 0) + n
+        weakref.finalize(t, _release, dev, n)  # dropped, overwritten or the module collected: the bytes come back
+    module.__dict__[slot] = (key, value, _fingerprint(w)) if CHECK_CACHE else (key, value)
 
 
 def _weight_get(self):
@@ -191,7 +253,10 @@ class QuantLinearConvBase(QuantInputBase):
         collected" mark) and the quantizers' fp32 amax copies.  The caches key on (data_ptr, _version) of the weight and
         of the quantizer buffers; call this after writing through `.data` or a raw pointer, which moves neither."""
         for k in _WEIGHT_CACHES:
-            self.__dict__.pop(k, None)
+            if k == "_weight_collect_key":
+                self.__dict__.pop(k, None)
+            else:
+                _cache_drop(self, k)
         for q in self.modules():
             if isinstance(q, TensorQuantizer):
                 q.__dict__.pop("_amax_f32", None)
@@ -262,7 +327,7 @@ class _QuantLinear(QuantLinearConvBase):
         q = self.weight_quantizer
         qk = q.cache_key() if isinstance(q, TensorQuantizer) else None
         if qk is None:
-            self.__dict__.pop("_wq_cache", None)
+            _cache_drop(self, "_wq_cache")
             with self.quantize_weight():
                 return self.weight
         key = (w.data_ptr(), w._version, tuple(w.shape), w.dtype, qk)
