@@ -65,7 +65,7 @@ def parse():
     p.add_argument("--e2e-steps", type=int, default=2)
     p.add_argument("--seqs", type=int, default=512, help="model-level calibration set (sequences of 2048 tokens)")
     p.add_argument("--micro-batch", type=int, default=None, help="model-level micro-batch (default 8; 70b: 4)")
-    p.add_argument("--model-presets", default=None, help="comma list for the model-level leg (default nvfp4,fp8; 70b: nvfp4)")
+    p.add_argument("--model-presets", default=None, help="comma list for the model-level leg (default nvfp4,fp8,hist; 70b: nvfp4,hist)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-workloads", action="store_true")
@@ -575,7 +575,7 @@ def main():
     if not a.no_model_level:
         import model_level as ml
 
-        presets = tuple((a.model_presets or ("nvfp4" if a.model == "70b" else "nvfp4,fp8")).split(","))
+        presets = tuple((a.model_presets or ("nvfp4,hist" if a.model == "70b" else "nvfp4,fp8,hist")).split(","))
         mb = a.micro_batch or (4 if a.model == "70b" else 8)
         with Clocks(local) as mclk:
             res = ml.run(a.model, presets, a.seqs, mb, 2048, device, rank, world)

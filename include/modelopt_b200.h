@@ -148,7 +148,7 @@ int mo_hist(const void* x, int64_t n, int dtype, const float* range_max, int64_t
  *   first = 0 : begin = bin x under the current range and fold max|x| in the same read;  end = if the max exceeds the
  *               range, grow it exactly like histogram.py:121-126 (num_bins = ceil(x_max / width), range = last edge of
  *               arange(0, x_max + width, width); numerics = MO_NUMERICS_CPU evaluates arange like the CPU kernel, in
- *               fp64) and move the batch from the old bins to the new ones (two more reads of x, only on such batches).
+ *               fp64) and move the batch from the old bins to the new ones (one more read of x, only on such batches).
  * With the all-reduce every rank takes the same decisions, so its counts are bin-compatible with every other rank's and
  * their SUM equals one process calibrating on the concatenated batches.  A range needing more than `capacity` bins, or
  * a non-finite max, sets a flag in state[MO_HIST_FLAGS] and freezes the state (later launches are no-ops); the caller
@@ -165,6 +165,9 @@ int mo_hist_collect_begin(const void* x, int64_t n, int dtype, int32_t* state, u
                           int64_t smem_bins_hint, int skip_zeros, int first, void* stream);
 int mo_hist_collect_end(const void* x, int64_t n, int dtype, int32_t* state, uint64_t* counts, int64_t capacity,
                         int64_t smem_bins_hint, int skip_zeros, int first, int init_bins, int numerics, void* stream);
+/* begin + end in one call (single process: nothing to exchange between the halves). */
+int mo_hist_collect(const void* x, int64_t n, int dtype, int32_t* state, uint64_t* counts, int64_t capacity,
+                    int64_t smem_bins_hint, int skip_zeros, int first, int init_bins, int numerics, void* stream);
 
 /* _compute_amax_percentile (histogram.py:328-343): *idx_out (device) = searchsorted(cumsum(hist/total),
  * percentile/100) in fp64, numpy's summation order; the amax is edges[idx]. */

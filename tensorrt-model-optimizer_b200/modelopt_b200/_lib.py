@@ -37,6 +37,7 @@ SIGNATURES = {
     "mo_hist": [_p, _i64, _i, _p, _i64, _p, _p, _i, _p],
     "mo_hist_collect_begin": [_p, _i64, _i, _p, _p, _i64, _i64, _i, _i, _p],
     "mo_hist_collect_end": [_p, _i64, _i, _p, _p, _i64, _i64, _i, _i, _i, _i, _p],
+    "mo_hist_collect": [_p, _i64, _i, _p, _p, _i64, _i64, _i, _i, _i, _i, _p],
     "mo_hist_percentile": [_p, _i64, C.c_double, _p, _p],
     "mo_hist_mse": [_p, _p, _i64, _i, _i, _i, _i, _i, _i, _p, _p, _p],
     "mo_hist_entropy_scratch_bytes": [_i64, _i, _i],

@@ -95,14 +95,19 @@ class HistogramCalibrator(_Calibrator):
         else:
             self._poll()  # a finished read-back of an earlier batch: learn the bin count, report a frozen state
         hint = self._hint()
-        ops.hist_collect_begin(x, self._state, self._buf, hint, self._skip_zeros, first)
-        if self._group_size() > 1:  # one word; every rank then takes the same grow / no-grow decision
+        if self._group_size() > 1:
+            ops.hist_collect_begin(x, self._state, self._buf, hint, self._skip_zeros, first)
+            # one word; every rank then takes the same grow / no-grow decision
             dist.all_reduce(self._state[_BATCH_AMAX:_BATCH_AMAX + 1], op=dist.ReduceOp.MAX, group=self.dp_group)
-        ops.hist_collect_end(x, self._state, self._buf, hint, self._skip_zeros, first, self._init_bins, self.numerics)
+            ops.hist_collect_end(x, self._state, self._buf, hint, self._skip_zeros, first, self._init_bins, self.numerics)
+        else:
+            ops.hist_collect(x, self._state, self._buf, hint, self._skip_zeros, first, self._init_bins, self.numerics)
         self._synced = False
         self._edges_cache = None
         self._snap_valid = False
-        if self._pending is None:  # asynchronous read-back: 64 bytes, looked at by a later collect
+        self._n_collect = getattr(self, "_n_collect", 0) + 1
+        # asynchronous read-back (64 bytes), looked at by a later collect: after the first batches, then every 8th
+        if self._pending is None and (self._n_collect <= 2 or self._n_collect % 8 == 0):
             if self._host is None:
                 self._host = torch.empty(_STATE_WORDS, dtype=torch.int32).pin_memory()
             self._host.copy_(self._state, non_blocking=True)

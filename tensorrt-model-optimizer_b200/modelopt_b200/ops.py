@@ -488,7 +488,18 @@ def hist_collect_end(x, state, counts, smem_bins_hint, skip_zeros, first, init_b
         _launched(_lib.load().mo_hist_collect_end(x.data_ptr(), x.numel(), _code(x), state.data_ptr(), counts.data_ptr(),
                                                   counts.numel(), int(smem_bins_hint), int(bool(skip_zeros)),
                                                   int(bool(first)), int(init_bins), _mode(numerics), _stream(x)),
-                  "mo_hist_collect_end", n=2 if first else 3)
+                  "mo_hist_collect_end", n=2)
+
+
+def hist_collect(x, state, counts, smem_bins_hint, skip_zeros, first, init_bins, numerics=None):
+    """begin + end in one C call (no data-parallel exchange between the halves)."""
+    _cuda(x, "hist_collect")
+    assert state.dtype == torch.int32 and state.numel() >= 16 and state.device == x.device
+    assert counts.dtype == torch.int64 and counts.is_contiguous() and counts.device == x.device and x.is_contiguous()
+    with _dev(x):
+        _launched(_lib.load().mo_hist_collect(x.data_ptr(), x.numel(), _code(x), state.data_ptr(), counts.data_ptr(),
+                                              counts.numel(), int(smem_bins_hint), int(bool(skip_zeros)), int(bool(first)),
+                                              int(init_bins), _mode(numerics), _stream(x)), "mo_hist_collect", n=3)
 
 
 def hist_percentile_index(counts, percentile: float) -> torch.Tensor:

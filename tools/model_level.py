@@ -17,6 +17,7 @@ Stand-alone:  python tools/model_level.py [--model 8b|70b|tiny] [--preset nvfp4|
 from __future__ import annotations
 
 import argparse
+import copy
 import json
 import os
 import sys
@@ -237,11 +238,34 @@ def run(model_name="8b", presets=("nvfp4",), n_seq_total=512, micro_batch=8, seq
         plain_equiv_s = plain["s_per_mb"] * feeder.n_mb  # plain forward over the rank's whole share
 
         # ---- the user's call: quantize(model, cfg, forward_loop) ----
-        cfg = getattr(qcfg, PRESETS[preset])
         launches0 = ops.LAUNCHES[0]
         feeder.h2d = feeder.d2h = 0
         torch.cuda.reset_peak_memory_stats(device)
-        _, quant_s, quant_wall = _timed(lambda: mtq.quantize(model, cfg, feeder.loop), device, world)
+        if preset == "hist":
+            # histogram calibration of every linear input (INT8 per tensor, entropy search): the reference's explicit flow
+            # enable_stats_collection -> forward_loop -> finish_stats_collection(method="entropy") (model_calib.py:1128-1167,
+            # calib/histogram.py); data-parallel: the batch maximum all-reduced(MAX) inside collect, counts all-reduced(SUM)
+            from modelopt_b200 import model_calib
+
+            hist_cfg = copy.deepcopy(qcfg.INT8_DEFAULT_CFG["quant_cfg"])
+            for e in hist_cfg:
+                if e["quantizer_name"] == "*weight_quantizer":
+                    e.pop("cfg", None)
+                    e["enable"] = False
+                elif e["quantizer_name"] == "*input_quantizer":
+                    e["cfg"] = {"num_bits": 8, "axis": None, "calibrator": "histogram"}
+
+            def hist_calibrate():
+                mtq.replace_quant_module(model)
+                mtq.set_quantizer_by_cfg(model, hist_cfg)
+                model_calib.enable_stats_collection(model)
+                feeder.loop(model)
+                model_calib.finish_stats_collection(model, method="entropy")
+
+            _, quant_s, quant_wall = _timed(hist_calibrate, device, world)
+        else:
+            cfg = getattr(qcfg, PRESETS[preset])
+            _, quant_s, quant_wall = _timed(lambda: mtq.quantize(model, cfg, feeder.loop), device, world)
         launches = ops.LAUNCHES[0] - launches0
         h2d, d2h = feeder.h2d, feeder.d2h
         quantizers = [m for m in model.modules() if isinstance(m, TensorQuantizer)]
@@ -260,10 +284,12 @@ def run(model_name="8b", presets=("nvfp4",), n_seq_total=512, micro_batch=8, seq
         q_host_s, n_calls = host_us_per_quantizer_call(model, device)
         peak_mem = torch.cuda.max_memory_allocated(device)
         out[preset] = {
-            "api": "modelopt_b200.quantize(model, %s, forward_loop)" % PRESETS[preset],
+            "api": ("enable_stats_collection -> forward_loop -> finish_stats_collection(method='entropy'), "
+                    "HistogramCalibrator (INT8 per tensor) on every quantized linear's input" if preset == "hist"
+                    else "modelopt_b200.quantize(model, %s, forward_loop)" % PRESETS[preset]),
             "model": f"{NAMES[model_name]} random-init bf16, {n_params(model) / 1e9:.2f} B parameters"
                      + (f" ({layers} layers)" if layers else ""),
-            "preset": PRESETS[preset],
+            "preset": PRESETS.get(preset, "INT8 activations, histogram calibrator, entropy"),
             "calibration_set": f"{n_seq_total} sequences x {seq_len} tokens, micro-batch {micro_batch}, "
                                f"{n_seq} sequences per rank (strong scaling over {world} ranks)",
             "tokens": tokens_all,
