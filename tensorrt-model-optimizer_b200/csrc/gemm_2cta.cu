@@ -1,7 +1,12 @@
 // Quant-aware linear (bf16 / f16 operands) on CTA PAIRS (tcgen05 cta_group::2): the math of csrc/gemm.cu's plain and loss
 // modes with the 256 x 256 tile of a pair of SMs.  Each CTA of the 2-CTA cluster holds its own 128 rows of A and HALF of the
 // B tile, so per K step a CTA fills and reads 32 KB of shared memory instead of 48 KB for its 128 x 256 of output - the
-// shared-memory bandwidth per SM is what bounds the single-CTA kernel - and the ring is 6 stages deep.
+// shared-memory bandwidth per SM is what bounds the single-CTA kernel - and the ring is 5 stages deep.
+// Epilogue (plain mode): TMEM -> registers -> bf16 -> a 128-byte-swizzled staging tile in shared memory -> TMA store
+// (cp.async.bulk.tensor ... global.shared::cta, SASS UTMASTG): each warp stages 32 rows x 64 columns at a time in one of
+// two 4 KB buffers, so the global writes are whole 128-byte rows issued by the copy engine instead of 16-byte stores
+// scattered over 32 rows per instruction, the epilogue warps never wait for a store, and ragged M / N are clipped by
+// the tensor map.  The loss mode reads `ref` and writes nothing, as before.
 // Protocol: see csrc/gemm_fp8_2cta.cu (same barriers; the leader's `full` barrier collects the bytes of both CTAs, the
 // MMA commit is multicast to both CTAs' `empty` / `tmem_full`, both epilogues arrive on the leader's `tmem_empty`).
 #include <type_traits>
@@ -14,15 +19,27 @@ namespace f16p {
 constexpr int BM = 128, BN = 256, BK = 64;    // per CTA: 128 rows of A, 128 of the 256 B rows; BK elements = 128 bytes
 constexpr int BNH = BN / 2;
 constexpr int UMMA_K = 16;
-constexpr int kStages = 6;
+#ifndef MO_LAB_STAGES
+#define MO_LAB_STAGES 5
+#endif
+#ifndef MO_LAB_GROUPM
+#define MO_LAB_GROUPM 8
+#endif
+#ifndef MO_LAB_L2PROMO
+#define MO_LAB_L2PROMO CU_TENSOR_MAP_L2_PROMOTION_L2_256B
+#endif
+constexpr int kStages = MO_LAB_STAGES;
+constexpr int kEpiCols = 64;                  // columns per staged chunk: 64 bf16 = one 128-byte swizzle row
+constexpr uint32_t kEpiBytes = 32 * kEpiCols * 2;  // one warp's chunk: 32 rows x 128 bytes
 constexpr int kThreadsG = 192;
 constexpr uint32_t kABytes = BM * BK * 2, kBBytes = BNH * BK * 2, kStageBytes = kABytes + kBBytes;
-constexpr int kGroupM = 8;                    // 8 pair-tiles of 256 rows
+constexpr int kGroupM = MO_LAB_GROUPM;        // pair-tiles of 256 rows walked together (L2 residency of their A rows)
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // clears the CTA-rank bit of a shared::cluster address (leader's copy)
 
 struct Smem {
   uint8_t a[kStages][kABytes];
   uint8_t b[kStages][kBBytes];
+  uint8_t epi[4][2][kEpiBytes];  // per epilogue warp: two staging chunks (1024-byte aligned: the swizzle atom)
   uint64_t full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
   uint32_t tmem_base;
 };
@@ -70,6 +87,7 @@ __device__ __forceinline__ void tile_coord(int tile, int tiles_m, int tiles_n, i
 template <bool kHalf, bool kLoss>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(f16p::kThreadsG, 1)
 linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                   const __grid_constant__ CUtensorMap map_out,
                    const void* __restrict__ bias_v, void* __restrict__ out_v, const void* __restrict__ ref_v,
                    double* __restrict__ loss_acc, double loss_scale, int M, int N, int K) {
   using namespace f16p;
@@ -86,6 +104,7 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    if constexpr (!kLoss) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
     for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&s.tmem_full[i], 1); mbar_init(&s.tmem_empty[i], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -112,9 +131,13 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         const int m0 = m_blk * 2 * BM + (int)rank * BM, n0 = n_blk * BN + (int)rank * BNH;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&s.empty[stage], phase ^ 1);
+#if defined(MO_GEMM_EXP) && (MO_GEMM_EXP & 1)  // lab: no operand traffic at all (the MMAs read stale shared memory)
+          if (leader) mbar_expect_tx(&s.full[stage], 0);
+#else
           if (leader) mbar_expect_tx(&s.full[stage], 2 * kStageBytes);  // bytes of both CTAs land on this barrier
           tma_load_2d_pair16(s.a[stage], &map_a, &s.full[stage], kb * BK, m0);
           tma_load_2d_pair16(s.b[stage], &map_b, &s.full[stage], kb * BK, n0);
+#endif
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
       }
@@ -162,29 +185,29 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       const int row = m_blk * 2 * BM + (int)rank * BM + quarter * 32 + lane;
       const int n0 = n_blk * BN;
       const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
+      if constexpr (kLoss) {
 #pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
-        uint32_t r[32];
-        tmem_ld32(taddr + (uint32_t)c0, r);
-        if (row < M) {
+        for (int c0 = 0; c0 < BN; c0 += 32) {
+          uint32_t r[32];
+          tmem_ld32(taddr + (uint32_t)c0, r);
+          if (row < M) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 8) {
-            const int col = n0 + c0 + j;
-            if (col < N) {
-              float f[8];
+            for (int j = 0; j < 32; j += 8) {
+              const int col = n0 + c0 + j;
+              if (col < N) {
+                float f[8];
 #pragma unroll
-              for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
-              if (bias != nullptr) {
-                const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
-                const T* bp = reinterpret_cast<const T*>(&bv);
+                for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
+                if (bias != nullptr) {
+                  const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
+                  const T* bp = reinterpret_cast<const T*>(&bv);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) f[i] = __fadd_rn(f[i], Elem<T>::load(bp + i));
-              }
-              uint4 o;
-              T* op = reinterpret_cast<T*>(&o);
+                  for (int i = 0; i < 8; ++i) f[i] = __fadd_rn(f[i], Elem<T>::load(bp + i));
+                }
+                uint4 o;
+                T* op = reinterpret_cast<T*>(&o);
 #pragma unroll
-              for (int i = 0; i < 8; ++i) Elem<T>::store(op + i, f[i]);
-              if constexpr (kLoss) {
+                for (int i = 0; i < 8; ++i) Elem<T>::store(op + i, f[i]);
                 const uint4 rv = __ldg(reinterpret_cast<const uint4*>(ref + (int64_t)row * N + col));
                 const T* rp = reinterpret_cast<const T*>(&rv);
 #pragma unroll
@@ -194,10 +217,66 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                   const float d = Elem<T>::load(&dt);
                   loss = __fmaf_rn(d, d, loss);
                 }
-              } else {
-                *reinterpret_cast<uint4*>(out + (int64_t)row * N + col) = o;
               }
             }
+          }
+        }
+      } else {
+        // plain mode: stage 32 rows x 64 columns per warp in swizzled shared memory, then one TMA store per chunk
+        const int row0 = m_blk * 2 * BM + (int)rank * BM + quarter * 32;
+#pragma unroll 1
+        for (int c0 = 0; c0 < BN; c0 += kEpiCols) {
+          uint8_t* buf = s.epi[quarter][(c0 / kEpiCols) & 1];
+          // the TMA store that last read this buffer (two chunks ago) must have finished reading it
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
+          __syncwarp();
+#if defined(MO_GEMM_EXP) && (MO_GEMM_EXP & 2)  // lab: no epilogue work (accumulators are dropped)
+          const bool live = false;
+#else
+          const bool live = n0 + c0 < N && row0 < M;  // a chunk wholly outside the tensor is neither staged nor stored
+#endif
+          if (live) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              uint32_t r[32];
+              tmem_ld32(taddr + (uint32_t)(c0 + 32 * h), r);
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                const int col = n0 + c0 + 32 * h + j;
+                float f[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
+                if (bias != nullptr && col < N) {
+                  const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
+                  const T* bp = reinterpret_cast<const T*>(&bv);
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) f[i] = __fadd_rn(f[i], Elem<T>::load(bp + i));
+                }
+                uint4 o;
+                T* op = reinterpret_cast<T*>(&o);
+#pragma unroll
+                for (int i = 0; i < 8; ++i) Elem<T>::store(op + i, f[i]);
+                const int chunk = 4 * h + (j >> 3);  // 16-byte chunk of the 128-byte row; SWIZZLE_128B: chunk ^= row % 8
+#if defined(MO_GEMM_EXP) && (MO_GEMM_EXP & 4)  // lab: TMEM is read, nothing is staged or stored
+                if (o.x == 0x12345678u && o.y == 0x9abcdef0u) *reinterpret_cast<uint4*>(buf) = o;
+#else
+                *reinterpret_cast<uint4*>(buf + lane * 128 + ((chunk ^ (lane & 7)) << 4)) = o;
+#endif
+              }
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the TMA
+          }
+          __syncwarp();
+          if (lane == 0) {
+#if defined(MO_GEMM_EXP) && (MO_GEMM_EXP & 4)
+            if (false)
+#else
+            if (live)
+#endif
+              asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+                           ::"l"(&map_out), "r"(smem_u32(buf)), "r"(n0 + c0), "r"(row0)
+                           : "memory");
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");  // one group per chunk keeps the wait count exact
           }
         }
       }
@@ -211,6 +290,8 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) dloss += __shfl_xor_sync(0xffffffffu, dloss, o);
       if (lane == 0 && dloss != 0.0) atomicAdd(loss_acc, dloss * loss_scale);
+    } else {
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // every store has landed before exit
     }
   }
 
@@ -232,13 +313,28 @@ static bool make_map16_pair(CUtensorMap* m, const void* base, int64_t rows, int6
   const cuuint32_t estr[2] = {1, 1};
   const CUresult r = fn(m, half ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
                         const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                        CU_TENSOR_MAP_SWIZZLE_128B, MO_LAB_L2PROMO, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return false; }
   return true;
 }
 
+// output [M, N] row-major, stored in boxes of 32 rows x 64 columns (one warp's staged chunk), 128-byte swizzle
+static bool make_map16_out(CUtensorMap* m, void* base, int64_t M, int64_t N, bool half) {
+  EncodeTiledFn fn = encode_fn();
+  if (fn == nullptr) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return false; }
+  const cuuint64_t dims[2] = {(cuuint64_t)N, (cuuint64_t)M};
+  const cuuint64_t strides[1] = {(cuuint64_t)N * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)f16p::kEpiCols, 32u};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(m, half ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, base, dims, strides,
+                        box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled (output) failed (CUresult %d)", (int)r); return false; }
+  return true;
+}
+
 template <bool kHalf, bool kLoss>
-static int linear_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const void* bias, void* out, const void* ref,
+static int linear_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const void* bias, void* out, const void* ref,
                               double* loss_acc, int M, int N, int K, cudaStream_t s) {
   auto kern = linear_pair_kernel<kHalf, kLoss>;
   const int smem = (int)sizeof(f16p::Smem) + 1024;
@@ -250,7 +346,7 @@ static int linear_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, cons
   }
   const int tiles = ((M + 2 * f16p::BM - 1) / (2 * f16p::BM)) * ((N + f16p::BN - 1) / f16p::BN);
   const int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
-  kern<<<2 * pairs, f16p::kThreadsG, smem, s>>>(ma, mb, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), M, N, K);
+  kern<<<2 * pairs, f16p::kThreadsG, smem, s>>>(ma, mb, mo, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), M, N, K);
   return check_launch("mo_linear_pair");
 }
 
@@ -270,12 +366,14 @@ extern "C" int mo_linear_pair(const void* x, const void* w, const void* bias, vo
   auto mis = [](const void* p) { return p && (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
   if (mis(x) || mis(w) || mis(bias) || mis(out) || mis(ref)) { set_error("mo_linear_pair: pointers must be 16-byte aligned"); return MO_ERR_ARG; }
   const bool half = dtype == MO_F16;
-  CUtensorMap ma, mb;
+  CUtensorMap ma, mb, mo;
   if (!make_map16_pair(&ma, x, M, K, f16p::BM, half) || !make_map16_pair(&mb, w, N, K, f16p::BNH, half)) return MO_ERR_ARG;
+  if (loss) mo = ma;  // unused in loss mode (nothing is written)
+  else if (!make_map16_out(&mo, out, M, N, half)) return MO_ERR_ARG;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int m = (int)M, n = (int)N, k = (int)K;
-  if (half) return loss ? linear_pair_launch<true, true>(ma, mb, bias, out, ref, loss_acc, m, n, k, s)
-                        : linear_pair_launch<true, false>(ma, mb, bias, out, ref, loss_acc, m, n, k, s);
-  return loss ? linear_pair_launch<false, true>(ma, mb, bias, out, ref, loss_acc, m, n, k, s)
-              : linear_pair_launch<false, false>(ma, mb, bias, out, ref, loss_acc, m, n, k, s);
+  if (half) return loss ? linear_pair_launch<true, true>(ma, mb, mo, bias, out, ref, loss_acc, m, n, k, s)
+                        : linear_pair_launch<true, false>(ma, mb, mo, bias, out, ref, loss_acc, m, n, k, s);
+  return loss ? linear_pair_launch<false, true>(ma, mb, mo, bias, out, ref, loss_acc, m, n, k, s)
+              : linear_pair_launch<false, false>(ma, mb, mo, bias, out, ref, loss_acc, m, n, k, s);
 }
