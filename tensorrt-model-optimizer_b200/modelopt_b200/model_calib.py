@@ -276,8 +276,27 @@ def sync_histograms(model: nn.Module, group=None):
         off += n
 
 
-def disable_pre_quant_scale_and_resmooth(*a, **k):  # pragma: no cover
-    raise NotImplementedError("modelopt_b200: resmoothing is not implemented")
+@torch.no_grad()
+def disable_pre_quant_scale_and_resmooth(linear: nn.Module, delete_pre_quant_scale: bool = False):
+    """model_calib.py:1169-1204: fold the input quantizer's pre_quant_scale back into the weight (W <- dtype(W * s)),
+    re-calibrate the weight quantizer and switch the scale off; the fold and the new weight amax are ONE kernel
+    (mo_scale_cols_amax) for per-row / per-tensor weight quantizers."""
+    from .utils import is_quantized_linear
+
+    assert is_quantized_linear(linear), "Only quantized linear modules are supported"
+    iq = linear.input_quantizer
+    assert iq._enable_pre_quant_scale, "pre_quant_scale should be enabled first!"
+    assert hasattr(iq, "_pre_quant_scale"), "pre_quant_scale should be available"
+    _apply_weight_pre_quant_scale(linear, iq._pre_quant_scale.to(torch.float32))
+    # the scale is kept (it may be useful later) but disabled
+    iq._enable_pre_quant_scale = False
+    if iq.amax is not None:
+        assert hasattr(iq, "_amax_for_smoothing")
+        w = linear._parameters["weight"]
+        iq.amax = iq._amax_for_smoothing.amax().to(device=w.device, dtype=w.dtype)
+    if delete_pre_quant_scale:
+        delattr(iq, "_pre_quant_scale")
+        iq._enable_pre_quant_scale = False
 
 
 # =================================================================================================
@@ -531,6 +550,7 @@ def _apply_weight_pre_quant_scale(linear, pre_quant_scale):
         mode = "row" if q.axis in (0, (0,)) else ("tensor" if q.axis is None else None)
     if not (w.is_cuda and w.dim() == 2 and w.is_contiguous()):
         w.data.copy_((w * s[None, :]).to(w.dtype))
+        linear.invalidate_weight_cache()  # `.data.copy_` does not move the weight's version counter
         _recalibrate_weight(linear)
         return
     if mode is None:

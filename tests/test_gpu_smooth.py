@@ -195,3 +195,49 @@ def test_awq_lite_vs_reference_golden():
         torch.testing.assert_close(m.state_dict()[k].cpu(), torch.from_numpy(g[f"{name}|weight_after|{k}"]),
                                    rtol=1e-5, atol=1e-7)
     torch.testing.assert_close(out.cpu(), torch.from_numpy(g[f"{name}|out"]), rtol=5e-2, atol=5e-2)
+
+
+@pytest.mark.parametrize("name", ["INT8_SMOOTHQUANT_CFG", "INT4_AWQ_CFG"])
+def test_disable_pre_quant_scale_and_resmooth_vs_reference_golden(name):
+    """model_calib.py:1169-1204 against the reference's CPU run (tests/golden/resmooth_cpu.npz, oracle/gen_golden_resmooth.py):
+    folded weights bit for bit, re-calibrated weight amax, input amax, and the scale kept-but-disabled / deleted."""
+    import modelopt_b200 as mtq
+    from modelopt_b200 import ops
+    from modelopt_b200.model_calib import disable_pre_quant_scale_and_resmooth
+
+    q, g = load_golden("quantize_cpu.npz"), load_golden("resmooth_cpu.npz")
+    m = _tiny(q)
+    batches = [torch.from_numpy(q[f"batch{i}"]).cuda() for i in range(3)]
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        with ops.numerics("cpu"):
+            mtq.quantize(m, copy.deepcopy(getattr(mtq, name)), lambda model: [model(b) for b in batches])
+            for idx, delete in ((0, False), (2, True)):
+                disable_pre_quant_scale_and_resmooth(m[idx], delete_pre_quant_scale=delete)
+            out = m(torch.from_numpy(q["test"]).cuda())
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    seen = 0
+    for n, mod in m.named_modules():
+        if f"{name}|{n}|has_pqs" not in g.files:
+            continue
+        assert hasattr(mod, "_pre_quant_scale") == bool(g[f"{name}|{n}|has_pqs"]), n
+        assert bool(mod._enable_pre_quant_scale) == bool(g[f"{name}|{n}|pqs_enabled"]), n
+        if f"{name}|{n}|_amax" in g.files:
+            want = torch.from_numpy(g[f"{name}|{n}|_amax"])
+            got = mod._amax.float().cpu()
+            assert got.shape == want.shape, n
+            if name == "INT4_AWQ_CFG":  # the AWQ scale itself carries CUDA-vs-CPU pow() ulps (test_awq_lite_vs_reference_golden)
+                torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-6)
+            else:
+                assert torch.equal(got, want), n
+            seen += 1
+    assert seen >= 2
+    for k in ("0.weight", "2.weight"):
+        want, got = torch.from_numpy(g[f"{name}|weight|{k}"]), m.state_dict()[k].cpu()
+        if name == "INT4_AWQ_CFG":
+            torch.testing.assert_close(got, want, rtol=1e-4, atol=1e-6)
+        else:
+            assert torch.equal(got, want), k
+    torch.testing.assert_close(out.cpu(), torch.from_numpy(g[f"{name}|out"]), rtol=2e-2, atol=2e-2)
