@@ -16,31 +16,49 @@
 namespace mo {
 
 namespace f16p {
-constexpr int BM = 128, BN = 256, BK = 64;    // per CTA: 128 rows of A, 128 of the 256 B rows; BK elements = 128 bytes
+// kMH = 128-row M blocks per CTA.  1: pair tile 256 x 256 (each CTA: 128 rows of A + 128 of the 256 B rows per stage, the
+// two TMEM accumulators alternate between tiles).  2: pair tile 512 x 256 - each CTA holds 256 rows of A and issues two
+// M = 256 MMAs per K step against the same B tile, one per accumulator: per flop 0.75x the bytes through L2 and shared
+// memory (112 KB per 1024 tensor clocks per SM instead of 64 KB per 512), which is what bounds the 256 x 256 form (ncu
+// side by side with cuBLAS's nvjet 256x256 2cta kernel, profiles/r02_gemm_vs_cublas.txt: 124 M vs 76 M L2 read sectors,
+// tensor pipe 82.5 % vs 88.2 % active).  Both accumulators belong to the same tile, so its epilogue is only
+// overlapped with the first K steps of the next tile's other half.
+#ifndef MO_LAB_MH
+#define MO_LAB_MH 0  /* 0 = chosen per call by the launcher; 1 / 2 force one form (tools/gemm_lab.py) */
+#endif
+constexpr int BM = 128, BN = 256, BK = 64;    // MMA M per CTA, pair-tile N, K step (BK elements = 128 bytes)
 constexpr int BNH = BN / 2;
 constexpr int UMMA_K = 16;
-#ifndef MO_LAB_STAGES
-#define MO_LAB_STAGES 5
-#endif
 #ifndef MO_LAB_GROUPM
-#define MO_LAB_GROUPM 8
+#define MO_LAB_GROUPM 0  /* 0 = chosen per shape by the launcher */
 #endif
 #ifndef MO_LAB_L2PROMO
 #define MO_LAB_L2PROMO CU_TENSOR_MAP_L2_PROMOTION_L2_256B
 #endif
-constexpr int kStages = MO_LAB_STAGES;
 constexpr int kEpiCols = 64;                  // columns per staged chunk: 64 bf16 = one 128-byte swizzle row
 constexpr uint32_t kEpiBytes = 32 * kEpiCols * 2;  // one warp's chunk: 32 rows x 128 bytes
 constexpr int kThreadsG = 192;
-constexpr uint32_t kABytes = BM * BK * 2, kBBytes = BNH * BK * 2, kStageBytes = kABytes + kBBytes;
-constexpr int kGroupM = MO_LAB_GROUPM;        // pair-tiles of 256 rows walked together (L2 residency of their A rows)
+constexpr uint32_t kBBytes = BNH * BK * 2;
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // clears the CTA-rank bit of a shared::cluster address (leader's copy)
 
+template <int kMH>
+struct Cfg {
+  static constexpr int BMC = BM * kMH;                 // A rows per CTA and tile
+#ifdef MO_LAB_STAGES
+  static constexpr int kStages = MO_LAB_STAGES;
+#else
+  static constexpr int kStages = kMH == 2 ? 4 : 5;     // 48 KB / 32 KB stages: 192 KB / 160 KB of the ring
+#endif
+  static constexpr uint32_t kABytes = BMC * BK * 2, kStageBytes = kABytes + kBBytes;
+};
+
+template <int kMH>
 struct Smem {
-  uint8_t a[kStages][kABytes];
-  uint8_t b[kStages][kBBytes];
+  uint8_t a[Cfg<kMH>::kStages][Cfg<kMH>::kABytes];
+  uint8_t b[Cfg<kMH>::kStages][kBBytes];
   uint8_t epi[4][2][kEpiBytes];  // per epilogue warp: two staging chunks (1024-byte aligned: the swizzle atom)
-  uint64_t full[kStages], empty[kStages], tmem_full[2], tmem_empty[2];
+  uint64_t full[Cfg<kMH>::kStages], empty[Cfg<kMH>::kStages], tmem_full[2], tmem_empty[2];
+  uint64_t epi_bar[4][2];        // loss mode: a `ref` chunk has landed in epi[warp][buffer]
   uint32_t tmem_base;
 };
 
@@ -75,38 +93,43 @@ __device__ __forceinline__ void mbar_arrive_cta16(uint64_t* bar, uint32_t cta) {
                ::"r"(smem_u32(bar)), "r"(cta)
                : "memory");
 }
-__device__ __forceinline__ void tile_coord(int tile, int tiles_m, int tiles_n, int& m_blk, int& n_blk) {
-  const int per_group = kGroupM * tiles_n;
+// Tiles are walked in groups of `group_m` M-blocks x all N-blocks (M fastest), so that the pairs running at the same
+// time share A rows and B rows in L2.
+__device__ __forceinline__ void tile_coord(int tile, int tiles_m, int tiles_n, int group_m, int& m_blk, int& n_blk) {
+  const int per_group = group_m * tiles_n;
   const int g = tile / per_group, r = tile - g * per_group;
-  const int gm = min(kGroupM, tiles_m - g * kGroupM);
+  const int gm = min(group_m, tiles_m - g * group_m);
   n_blk = r / gm;
-  m_blk = g * kGroupM + (r - n_blk * gm);
+  m_blk = g * group_m + (r - n_blk * gm);
 }
 }  // namespace f16p
 
-template <bool kHalf, bool kLoss>
+template <bool kHalf, bool kLoss, int kMH>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(f16p::kThreadsG, 1)
 linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_out,
                    const void* __restrict__ bias_v, void* __restrict__ out_v, const void* __restrict__ ref_v,
-                   double* __restrict__ loss_acc, double loss_scale, int M, int N, int K) {
+                   double* __restrict__ loss_acc, double loss_scale, int M, int N, int K, int group_m) {
   using namespace f16p;
   using T = typename std::conditional<kHalf, __half, __nv_bfloat16>::type;
+  constexpr int BMC = Cfg<kMH>::BMC, kStages = Cfg<kMH>::kStages;
+  constexpr uint32_t kStageBytes = Cfg<kMH>::kStageBytes;
   extern __shared__ uint8_t smem_raw[];
-  Smem& s = *reinterpret_cast<Smem*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  Smem<kMH>& s = *reinterpret_cast<Smem<kMH>*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t rank = cluster_rank16();
   const bool leader = rank == 0;
-  const int tiles_m = (M + 2 * BM - 1) / (2 * BM), tiles_n = (N + BN - 1) / BN, num_tiles = tiles_m * tiles_n;
+  const int tiles_m = (M + 2 * BMC - 1) / (2 * BMC), tiles_n = (N + BN - 1) / BN, num_tiles = tiles_m * tiles_n;
   const int num_kb = (K + BK - 1) / BK;
   const int pair = blockIdx.x >> 1, num_pairs = gridDim.x >> 1;
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
-    if constexpr (!kLoss) asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_out) : "memory");
     for (int i = 0; i < kStages; ++i) { mbar_init(&s.full[i], 1); mbar_init(&s.empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&s.tmem_full[i], 1); mbar_init(&s.tmem_empty[i], 8); }
+    for (int i = 0; i < 8; ++i) mbar_init(&s.epi_bar[i >> 1][i & 1], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 1) {  // the same warp of both CTAs allocates the pair's TMEM (same address in both)
@@ -127,8 +150,8 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       uint32_t phase = 0;
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
         int m_blk, n_blk;
-        tile_coord(tile, tiles_m, tiles_n, m_blk, n_blk);
-        const int m0 = m_blk * 2 * BM + (int)rank * BM, n0 = n_blk * BN + (int)rank * BNH;
+        tile_coord(tile, tiles_m, tiles_n, group_m, m_blk, n_blk);
+        const int m0 = m_blk * 2 * BMC + (int)rank * BMC, n0 = n_blk * BN + (int)rank * BNH;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&s.empty[stage], phase ^ 1);
 #if defined(MO_GEMM_EXP) && (MO_GEMM_EXP & 1)  // lab: no operand traffic at all (the MMAs read stale shared memory)
@@ -147,86 +170,122 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       // kind::f16 descriptor: D = F32, A / B = BF16 (1) or F16 (0) K-major, N >> 3 at [17,23), M >> 4 at [24,29), M = 256
       const uint32_t fmt = kHalf ? 0u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
-      int stage = 0, acc = 0;
-      uint32_t phase = 0, acc_phase = 0;
+      int stage = 0;
+      uint32_t phase = 0, unit = 0;  // unit = accumulator use counter: slot = unit % 2, its barrier phase = (unit / 2) % 2
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
-        mbar_wait(&s.tmem_empty[acc], acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem + (uint32_t)(acc * BN);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&s.full[stage], phase);
           tc_fence_after();
           const uint64_t da = umma_desc(smem_u32(s.a[stage])), db = umma_desc(smem_u32(s.b[stage]));
 #pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k)
-            umma_f16_pair(d_tmem, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+          for (int h = 0; h < kMH; ++h) {
+            const uint32_t u = unit + (uint32_t)h, slot = u & 1u;
+            if (kb == 0) {  // the epilogue has drained this accumulator's previous use
+              mbar_wait(&s.tmem_empty[slot], ((u >> 1) & 1u) ^ 1u);
+              tc_fence_after();
+            }
+            const uint32_t d_tmem = tmem + slot * (uint32_t)BN;
+            const uint64_t dah = da + (uint64_t)((h * BM * BK * 2) >> 4);  // the CTA's h-th 128-row block of A
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k)
+              umma_f16_pair(d_tmem, dah + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+            if (kb == num_kb - 1) umma_commit_pair16(&s.tmem_full[slot]);
+          }
           umma_commit_pair16(&s.empty[stage]);
-          if (kb == num_kb - 1) umma_commit_pair16(&s.tmem_full[acc]);
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+        unit += kMH;
       }
     }
   } else {
     // ===== epilogue (both CTAs): warps 2..5 own TMEM lanes 32*(warp%4) .. +31 of their CTA's accumulator half =====
     const int quarter = warp & 3;
     const T* bias = static_cast<const T*>(bias_v);
-    T* out = static_cast<T*>(out_v);
-    const T* ref = static_cast<const T*>(ref_v);
-    int acc = 0;
-    uint32_t acc_phase = 0;
+    [[maybe_unused]] T* out = static_cast<T*>(out_v);
+    [[maybe_unused]] const T* ref = static_cast<const T*>(ref_v);
+    uint32_t unit = 0;  // accumulator use counter, as in the MMA issuer
+    uint32_t epi_uses = 0;       // loss mode: staging-buffer use counter (buffer = use % 2, barrier phase = (use / 2) % 2)
     float loss = 0.f;
     double dloss = 0.0;
     for (int tile = pair; tile < num_tiles; tile += num_pairs) {
       int m_blk, n_blk;
-      tile_coord(tile, tiles_m, tiles_n, m_blk, n_blk);
-      mbar_wait(&s.tmem_full[acc], acc_phase);
-      tc_fence_after();
-      const int row = m_blk * 2 * BM + (int)rank * BM + quarter * 32 + lane;
+      tile_coord(tile, tiles_m, tiles_n, group_m, m_blk, n_blk);
       const int n0 = n_blk * BN;
-      const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(acc * BN);
-      if constexpr (kLoss) {
 #pragma unroll 1
-        for (int c0 = 0; c0 < BN; c0 += 32) {
-          uint32_t r[32];
-          tmem_ld32(taddr + (uint32_t)c0, r);
-          if (row < M) {
+      for (int h = 0; h < kMH; ++h, ++unit) {  // the CTA's h-th 128-row block: one accumulator
+      const uint32_t acc = unit & 1u;
+      if constexpr (!kLoss) {
+        mbar_wait(&s.tmem_full[acc], (unit >> 1) & 1u);
+        tc_fence_after();
+      }
+      const int row = m_blk * 2 * BMC + (int)rank * BMC + h * BM + quarter * 32 + lane;
+      const uint32_t taddr = tmem + ((uint32_t)(quarter * 32) << 16) + acc * (uint32_t)BN;
+      if constexpr (kLoss) {
+        // loss mode: `ref` comes through the same staging buffers as the plain mode's output goes out - one TMA load per
+        // 32 x 64 chunk, two chunks in flight, the first two issued BEFORE the accumulator is waited for (ref does not
+        // depend on the MMAs) - instead of 16-byte loads scattered over 32 rows per instruction, whose latency sat in the
+        // open once both accumulators belonged to one tile.
+        const int row0 = m_blk * 2 * BMC + (int)rank * BMC + h * BM + quarter * 32;
+        auto fetch = [&](int c) {  // chunk c of this accumulator -> buffer (c & 1)
+          if (lane == 0) {
+            uint64_t* bar = &s.epi_bar[quarter][c & 1];
+            mbar_expect_tx(bar, kEpiBytes);
+            tma_load_2d(s.epi[quarter][c & 1], &map_out, bar, n0 + c * kEpiCols, row0);
+          }
+        };
+        fetch(0);  // both buffers are free: the previous accumulator's chunks were consumed in lock step
+        fetch(1);
+        mbar_wait(&s.tmem_full[acc], (unit >> 1) & 1u);
+        tc_fence_after();
+#pragma unroll 1
+        for (int c = 0; c < BN / kEpiCols; ++c, ++epi_uses) {
+          const uint8_t* buf = s.epi[quarter][c & 1];
+          mbar_wait(&s.epi_bar[quarter][c & 1], (epi_uses >> 1) & 1u);
 #pragma unroll
-            for (int j = 0; j < 32; j += 8) {
-              const int col = n0 + c0 + j;
-              if (col < N) {
-                float f[8];
+          for (int hh = 0; hh < 2; ++hh) {
+            uint32_t r[32];
+            tmem_ld32(taddr + (uint32_t)(c * kEpiCols + 32 * hh), r);
+            if (row < M) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
-                if (bias != nullptr) {
-                  const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
-                  const T* bp = reinterpret_cast<const T*>(&bv);
+              for (int j = 0; j < 32; j += 8) {
+                const int col = n0 + c * kEpiCols + 32 * hh + j;
+                if (col < N) {
+                  float f[8];
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) f[i] = __fadd_rn(f[i], Elem<T>::load(bp + i));
-                }
-                uint4 o;
-                T* op = reinterpret_cast<T*>(&o);
+                  for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
+                  if (bias != nullptr) {
+                    const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
+                    const T* bp = reinterpret_cast<const T*>(&bv);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) Elem<T>::store(op + i, f[i]);
-                const uint4 rv = __ldg(reinterpret_cast<const uint4*>(ref + (int64_t)row * N + col));
-                const T* rp = reinterpret_cast<const T*>(&rv);
+                    for (int i = 0; i < 8; ++i) f[i] = __fadd_rn(f[i], Elem<T>::load(bp + i));
+                  }
+                  uint4 o;
+                  T* op = reinterpret_cast<T*>(&o);
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                  T dt;
-                  Elem<T>::store(&dt, __fsub_rn(Elem<T>::load(op + i), Elem<T>::load(rp + i)));
-                  const float d = Elem<T>::load(&dt);
-                  loss = __fmaf_rn(d, d, loss);
+                  for (int i = 0; i < 8; ++i) Elem<T>::store(op + i, f[i]);
+                  const int chunk = 4 * hh + (j >> 3);  // SWIZZLE_128B: 16-byte chunk index ^ (row % 8)
+                  const uint4 rv = *reinterpret_cast<const uint4*>(buf + lane * 128 + ((chunk ^ (lane & 7)) << 4));
+                  const T* rp = reinterpret_cast<const T*>(&rv);
+#pragma unroll
+                  for (int i = 0; i < 8; ++i) {
+                    T dt;
+                    Elem<T>::store(&dt, __fsub_rn(Elem<T>::load(op + i), Elem<T>::load(rp + i)));
+                    const float d = Elem<T>::load(&dt);
+                    loss = __fmaf_rn(d, d, loss);
+                  }
                 }
               }
             }
           }
+          __syncwarp();  // every lane has read this buffer
+          if (c + 2 < BN / kEpiCols) fetch(c + 2);
         }
       } else {
         // plain mode: stage 32 rows x 64 columns per warp in swizzled shared memory, then one TMA store per chunk
-        const int row0 = m_blk * 2 * BM + (int)rank * BM + quarter * 32;
+        const int row0 = m_blk * 2 * BMC + (int)rank * BMC + h * BM + quarter * 32;
 #pragma unroll 1
         for (int c0 = 0; c0 < BN; c0 += kEpiCols) {
-          uint8_t* buf = s.epi[quarter][(c0 / kEpiCols) & 1];
+          uint8_t* buf = s.epi[quarter][(c0 / kEpiCols) & 1];  // BN / kEpiCols is even: the parity continues across halves
           // the TMA store that last read this buffer (two chunks ago) must have finished reading it
           if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");
           __syncwarp();
@@ -284,7 +343,7 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive_cta16(&s.tmem_empty[acc], 0);  // the leader's barrier collects both CTAs' 4 warps
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
     }
     if constexpr (kLoss) {
 #pragma unroll
@@ -333,21 +392,45 @@ static bool make_map16_out(CUtensorMap* m, void* base, int64_t M, int64_t N, boo
   return true;
 }
 
-template <bool kHalf, bool kLoss>
-static int linear_pair_launch(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mo, const void* bias, void* out, const void* ref,
+template <bool kHalf, bool kLoss, int kMH>
+static int linear_pair_launch(const void* x, const void* w, const void* bias, void* out, const void* ref,
                               double* loss_acc, int M, int N, int K, cudaStream_t s) {
-  auto kern = linear_pair_kernel<kHalf, kLoss>;
-  const int smem = (int)sizeof(f16p::Smem) + 1024;
+  CUtensorMap ma, mb, mo;
+  if (!make_map16_pair(&ma, x, M, K, f16p::Cfg<kMH>::BMC, kHalf) || !make_map16_pair(&mb, w, N, K, f16p::BNH, kHalf)) return MO_ERR_ARG;
+  // the [M, N] tensor the epilogue streams through its staging buffers: `out` (stored) or, in loss mode, `ref` (loaded)
+  if (!make_map16_out(&mo, kLoss ? const_cast<void*>(ref) : out, M, N, kHalf)) return MO_ERR_ARG;
+  auto kern = linear_pair_kernel<kHalf, kLoss, kMH>;
+  const int smem = (int)sizeof(f16p::Smem<kMH>) + 1024;
   static bool configured = false;
   if (!configured) {
     const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) { set_error("mo_linear_pair: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
     configured = true;
   }
-  const int tiles = ((M + 2 * f16p::BM - 1) / (2 * f16p::BM)) * ((N + f16p::BN - 1) / f16p::BN);
+  constexpr int BMC = f16p::Cfg<kMH>::BMC;
+  const int tiles = ((M + 2 * BMC - 1) / (2 * BMC)) * ((N + f16p::BN - 1) / f16p::BN);
   const int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
-  kern<<<2 * pairs, f16p::kThreadsG, smem, s>>>(ma, mb, mo, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), M, N, K);
+  // B200 measurements (profiles/r02_gemm_lab_mh2.txt): a weight that fits in L2 next to the streaming A rows (N <= 4096
+  // here) wants small groups - B stays resident, A is read once; wider weights want more M-blocks per pass over B
+  int group_m = MO_LAB_GROUPM;
+  if (group_m <= 0) group_m = (N <= 4096 ? 2 : 8) * (kMH == 2 ? 1 : 2);
+  kern<<<2 * pairs, f16p::kThreadsG, smem, s>>>(ma, mb, mo, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), M, N, K,
+                                                 group_m);
   return check_launch("mo_linear_pair");
+}
+
+// Which form runs (profiles/r02_gemm_lab_mh2.txt, r02_gemm_lab_loss.txt; sustained TFLOP/s at M = 16384 on B200):
+//   plain: the 512 x 256 pair tile everywhere it was measured (+5 % at K = 4096, +13 % at K = 14336);
+//   loss : its epilogue (TMEM read + `ref` from the staging buffers + the squared error) is about twice the plain one and
+//          both accumulators of the 512 x 256 form belong to one tile, so it is only hidden by a long K loop: 512 x 256
+//          from K = 8192 (+8 % at K = 14336), 256 x 256 below (where 512 x 256 measured -4 %).
+template <bool kHalf, bool kLoss>
+static int linear_pair_pick(const void* x, const void* w, const void* bias, void* out, const void* ref, double* loss_acc,
+                            int M, int N, int K, cudaStream_t s) {
+  int mh = MO_LAB_MH;
+  if (mh != 1 && mh != 2) mh = (kLoss && K < 8192) || M <= 256 ? 1 : 2;
+  return mh == 2 ? linear_pair_launch<kHalf, kLoss, 2>(x, w, bias, out, ref, loss_acc, M, N, K, s)
+                 : linear_pair_launch<kHalf, kLoss, 1>(x, w, bias, out, ref, loss_acc, M, N, K, s);
 }
 
 }  // namespace mo
@@ -366,14 +449,10 @@ extern "C" int mo_linear_pair(const void* x, const void* w, const void* bias, vo
   auto mis = [](const void* p) { return p && (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
   if (mis(x) || mis(w) || mis(bias) || mis(out) || mis(ref)) { set_error("mo_linear_pair: pointers must be 16-byte aligned"); return MO_ERR_ARG; }
   const bool half = dtype == MO_F16;
-  CUtensorMap ma, mb, mo;
-  if (!make_map16_pair(&ma, x, M, K, f16p::BM, half) || !make_map16_pair(&mb, w, N, K, f16p::BNH, half)) return MO_ERR_ARG;
-  if (loss) mo = ma;  // unused in loss mode (nothing is written)
-  else if (!make_map16_out(&mo, out, M, N, half)) return MO_ERR_ARG;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int m = (int)M, n = (int)N, k = (int)K;
-  if (half) return loss ? linear_pair_launch<true, true>(ma, mb, mo, bias, out, ref, loss_acc, m, n, k, s)
-                        : linear_pair_launch<true, false>(ma, mb, mo, bias, out, ref, loss_acc, m, n, k, s);
-  return loss ? linear_pair_launch<false, true>(ma, mb, mo, bias, out, ref, loss_acc, m, n, k, s)
-              : linear_pair_launch<false, false>(ma, mb, mo, bias, out, ref, loss_acc, m, n, k, s);
+  if (half) return loss ? linear_pair_pick<true, true>(x, w, bias, out, ref, loss_acc, m, n, k, s)
+                        : linear_pair_pick<true, false>(x, w, bias, out, ref, loss_acc, m, n, k, s);
+  return loss ? linear_pair_pick<false, true>(x, w, bias, out, ref, loss_acc, m, n, k, s)
+              : linear_pair_pick<false, false>(x, w, bias, out, ref, loss_acc, m, n, k, s);
 }

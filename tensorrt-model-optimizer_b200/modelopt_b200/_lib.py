@@ -9,7 +9,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libmodelopt_b200.so")
+LIB_PATH = os.environ.get("MODELOPT_B200_LIB") or os.path.join(_HERE, "lib", "libmodelopt_b200.so")
 
 MO_F32, MO_F16, MO_BF16 = 0, 1, 2
 MO_NUMERICS_GPU, MO_NUMERICS_CPU = 0, 1

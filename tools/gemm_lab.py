@@ -2,7 +2,9 @@
 overrides into tools/_lab/ (not part of the product library) and times them under sustained load against cuBLAS.
   build (CPU box):  python tools/gemm_lab.py build
   run (GPU box):    python tools/gemm_lab.py run
-bits: 1 = no operand traffic (MMAs on stale shared memory), 2 = no epilogue work."""
+-DMO_GEMM_EXP bits: 1 = no operand traffic (MMAs on stale shared memory), 2 = no epilogue work, 4 = TMEM read only;
+-DMO_LAB_MH=1|2 forces the 256 x 256 / 512 x 256 pair tile, -DMO_LAB_GROUPM / -DMO_LAB_STAGES / -DMO_LAB_L2PROMO override
+the tile walk, ring depth and L2 promotion; LAB_VARIANTS="name=flags;..." adds variants, LAB_LOSS=1 times the loss mode."""
 import ctypes as C
 import os
 import subprocess
@@ -11,7 +13,7 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LAB = os.path.join(ROOT, "tools", "_lab")
 CSRC = os.path.join(ROOT, "tensorrt-model-optimizer_b200", "csrc")
-VARIANTS = {"base": [], "no_tma": ["-DMO_GEMM_EXP=1"], "no_epi": ["-DMO_GEMM_EXP=2"], "no_both": ["-DMO_GEMM_EXP=3"]}
+VARIANTS = {"base": [], "mh1": ["-DMO_LAB_MH=1"], "mh2": ["-DMO_LAB_MH=2"]}
 for spec in os.environ.get("LAB_VARIANTS", "").split(";"):
     if spec:
         name, flags = spec.split("=", 1)
@@ -55,9 +57,15 @@ def run():
         flops = 2.0 * M * N * K
         stream = torch.cuda.current_stream().cuda_stream
         cands = {"cublas": lambda: torch.nn.functional.linear(x, w)}
+        loss_mode = os.environ.get("LAB_LOSS", "0") == "1"
+        ref = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
+        acc = torch.zeros(1, dtype=torch.float64, device="cuda")
         for name, lib in libs.items():
             def fn(lib=lib):
-                rc = lib.mo_linear_pair(x.data_ptr(), w.data_ptr(), None, out.data_ptr(), M, N, K, 2, None, None, stream)
+                if loss_mode:
+                    rc = lib.mo_linear_pair(x.data_ptr(), w.data_ptr(), None, None, M, N, K, 2, ref.data_ptr(), acc.data_ptr(), stream)
+                else:
+                    rc = lib.mo_linear_pair(x.data_ptr(), w.data_ptr(), None, out.data_ptr(), M, N, K, 2, None, None, stream)
                 assert rc == 0, rc
             cands[name] = fn
         res = {k: [] for k in cands}
