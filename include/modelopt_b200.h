@@ -422,11 +422,12 @@ int mo_gptq_block_nvfp4(const float* w, float* qw, float* err, const float* amax
  * out in out_dtype (bf16 / f16).  tcgen05.mma.kind::f8f6f4, fp32 accumulation.  K % 16 == 0, N % 8 == 0. */
 int mo_linear_fp8(const uint8_t* a, const uint8_t* b, const float* scale_a, const float* scale_b, const void* bias,
                   void* out, int64_t M, int64_t N, int64_t K, int out_dtype, void* stream);
-/* mo_linear (plain and loss modes) on CTA pairs: tcgen05 cta_group::2, 256 x 256 tile per 2-CTA cluster
- * (csrc/gemm_2cta.cu).  Same arguments, same results bit for bit; mo_linear routes large problems here. */
+/* mo_linear (plain and loss modes) on CTA pairs: tcgen05 cta_group::2, 512 x 256 (or, for short-K loss searches and
+ * small M, 256 x 256) tile per 2-CTA cluster, TMA-store epilogue (csrc/gemm_2cta.cu).  Same arguments, same results bit
+ * for bit. */
 int mo_linear_pair(const void* x, const void* w, const void* bias, void* out, int64_t M, int64_t N, int64_t K, int dtype,
                    const void* ref, double* loss_acc, void* stream);
-/* Same contract on CTA pairs (tcgen05 cta_group::2, 256 x 256 tile per 2-CTA cluster; csrc/gemm_fp8_2cta.cu). */
+/* Same contract on CTA pairs (tcgen05 cta_group::2, 512 x 256 or 256 x 256 tile per 2-CTA cluster; csrc/gemm_2cta.cu). */
 int mo_linear_fp8_pair(const uint8_t* a, const uint8_t* b, const float* scale_a, const float* scale_b, const void* bias,
                        void* out, int64_t M, int64_t N, int64_t K, int out_dtype, void* stream);
 

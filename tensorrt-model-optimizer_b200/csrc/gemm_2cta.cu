@@ -1,4 +1,5 @@
-// Quant-aware linear (bf16 / f16 operands) on CTA PAIRS (tcgen05 cta_group::2): the math of csrc/gemm.cu's plain and loss
+// Quant-aware linear on CTA PAIRS (tcgen05 cta_group::2), bf16 / f16 operands (kind::f16; mo_linear_pair) and E4M3 operands
+// with per-tensor scales (kind::f8f6f4; mo_linear_fp8_pair, the math of csrc/gemm_fp8.cu): the math of csrc/gemm.cu's plain and loss
 // modes with the 256 x 256 tile of a pair of SMs.  Each CTA of the 2-CTA cluster holds its own 128 rows of A and HALF of the
 // B tile, so per K step a CTA fills and reads 32 KB of shared memory instead of 48 KB for its 128 x 256 of output - the
 // shared-memory bandwidth per SM is what bounds the single-CTA kernel - and the ring is 5 stages deep.
@@ -7,8 +8,15 @@
 // two 4 KB buffers, so the global writes are whole 128-byte rows issued by the copy engine instead of 16-byte stores
 // scattered over 32 rows per instruction, the epilogue warps never wait for a store, and ragged M / N are clipped by
 // the tensor map.  The loss mode reads `ref` and writes nothing, as before.
-// Protocol: see csrc/gemm_fp8_2cta.cu (same barriers; the leader's `full` barrier collects the bytes of both CTAs, the
-// MMA commit is multicast to both CTAs' `empty` / `tmem_full`, both epilogues arrive on the leader's `tmem_empty`).
+// Protocol (per stage of the ring):
+//   * warp 0 of BOTH CTAs is a TMA producer: it waits on its own `empty[stage]`, then loads its A rows and its B half with
+//     cp.async.bulk.tensor...cta_group::2 whose complete_tx lands on the LEADER's `full[stage]` (peer bit of the barrier
+//     address cleared); the leader's producer posts the expect_tx for the bytes of both CTAs;
+//   * warp 1 lane 0 of the LEADER waits on `full[stage]` and issues tcgen05.mma.cta_group::2 (M = 256: TMEM lanes 0..127
+//     of each CTA), then tcgen05.commit...multicast::cluster arrives on `empty[stage]` of both CTAs; after an accumulator's
+//     last K step it commits to `tmem_full[acc]` of both CTAs;
+//   * warps 2..5 of both CTAs drain their own 128 rows of the accumulator and arrive on the LEADER's `tmem_empty[acc]`
+//     (8 arrivals: the peer's through mapa + mbarrier.arrive.shared::cluster).
 #include <type_traits>
 
 #include "tc_utils.cuh"
@@ -26,9 +34,10 @@ namespace f16p {
 #ifndef MO_LAB_MH
 #define MO_LAB_MH 0  /* 0 = chosen per call by the launcher; 1 / 2 force one form (tools/gemm_lab.py) */
 #endif
-constexpr int BM = 128, BN = 256, BK = 64;    // MMA M per CTA, pair-tile N, K step (BK elements = 128 bytes)
+constexpr int BM = 128, BN = 256;              // MMA M per CTA, pair-tile N
+constexpr int kRowBytes = 128;                // K step: one 128-byte swizzle row = 64 16-bit elements or 128 E4M3 codes
 constexpr int BNH = BN / 2;
-constexpr int UMMA_K = 16;
+constexpr int kMmaBytes = 32;                 // K bytes per tcgen05.mma (16 x 16-bit, 32 x 8-bit)
 #ifndef MO_LAB_GROUPM
 #define MO_LAB_GROUPM 0  /* 0 = chosen per shape by the launcher */
 #endif
@@ -38,7 +47,7 @@ constexpr int UMMA_K = 16;
 constexpr int kEpiCols = 64;                  // columns per staged chunk: 64 bf16 = one 128-byte swizzle row
 constexpr uint32_t kEpiBytes = 32 * kEpiCols * 2;  // one warp's chunk: 32 rows x 128 bytes
 constexpr int kThreadsG = 192;
-constexpr uint32_t kBBytes = BNH * BK * 2;
+constexpr uint32_t kBBytes = BNH * kRowBytes;
 constexpr uint32_t kPeerMask = 0xFEFFFFFFu;   // clears the CTA-rank bit of a shared::cluster address (leader's copy)
 
 template <int kMH>
@@ -49,7 +58,7 @@ struct Cfg {
 #else
   static constexpr int kStages = kMH == 2 ? 4 : 5;     // 48 KB / 32 KB stages: 192 KB / 160 KB of the ring
 #endif
-  static constexpr uint32_t kABytes = BMC * BK * 2, kStageBytes = kABytes + kBBytes;
+  static constexpr uint32_t kABytes = BMC * kRowBytes, kStageBytes = kABytes + kBBytes;
 };
 
 template <int kMH>
@@ -76,12 +85,19 @@ __device__ __forceinline__ void tma_load_2d_pair16(void* dst, const CUtensorMap*
       ::"r"(smem_u32(dst)), "l"(map), "r"(smem_u32(bar) & kPeerMask), "r"(c0), "r"(c1)
       : "memory");
 }
-__device__ __forceinline__ void umma_f16_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
-                                             uint32_t accumulate) {
-  asm volatile(
-      "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}"
-      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
-      : "memory");
+template <bool kFp8>
+__device__ __forceinline__ void umma_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                          uint32_t accumulate) {
+  if constexpr (kFp8)
+    asm volatile(
+        "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::2.kind::f8f6f4 [%0], %1, %2, %3, p;\n}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  else
+    asm volatile(
+        "{\n .reg .pred p;\n setp.ne.b32 p, %4, 0;\n tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
 }
 __device__ __forceinline__ void umma_commit_pair16(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
@@ -104,15 +120,18 @@ __device__ __forceinline__ void tile_coord(int tile, int tiles_m, int tiles_n, i
 }
 }  // namespace f16p
 
-template <bool kHalf, bool kLoss, int kMH>
+// kFp8: E4M3 operands (K in codes, 128 per row) and out = T(acc * (*scale_a * *scale_b) + bias); else bf16 / f16 operands.
+template <bool kHalf, bool kLoss, int kMH, bool kFp8>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(f16p::kThreadsG, 1)
 linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_out,
                    const void* __restrict__ bias_v, void* __restrict__ out_v, const void* __restrict__ ref_v,
-                   double* __restrict__ loss_acc, double loss_scale, int M, int N, int K, int group_m) {
+                   double* __restrict__ loss_acc, double loss_scale, const float* __restrict__ scale_a,
+                   const float* __restrict__ scale_b, int M, int N, int K, int group_m) {
   using namespace f16p;
   using T = typename std::conditional<kHalf, __half, __nv_bfloat16>::type;
   constexpr int BMC = Cfg<kMH>::BMC, kStages = Cfg<kMH>::kStages;
+  constexpr int BK = kFp8 ? kRowBytes : kRowBytes / 2;  // K elements per stage
   constexpr uint32_t kStageBytes = Cfg<kMH>::kStageBytes;
   extern __shared__ uint8_t smem_raw[];
   Smem<kMH>& s = *reinterpret_cast<Smem<kMH>*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -168,7 +187,8 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   } else if (warp == 1) {
     if (lane == 0 && leader) {  // ===== MMA issuer (leader CTA only) =====
       // kind::f16 descriptor: D = F32, A / B = BF16 (1) or F16 (0) K-major, N >> 3 at [17,23), M >> 4 at [24,29), M = 256
-      const uint32_t fmt = kHalf ? 0u : 1u;
+      // (kind::f8f6f4: A / B format 0 = E4M3)
+      const uint32_t fmt = (kFp8 || kHalf) ? 0u : 1u;
       const uint32_t idesc = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)((2 * BM) >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0, unit = 0;  // unit = accumulator use counter: slot = unit % 2, its barrier phase = (unit / 2) % 2
@@ -185,10 +205,10 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
               tc_fence_after();
             }
             const uint32_t d_tmem = tmem + slot * (uint32_t)BN;
-            const uint64_t dah = da + (uint64_t)((h * BM * BK * 2) >> 4);  // the CTA's h-th 128-row block of A
+            const uint64_t dah = da + (uint64_t)((h * BM * kRowBytes) >> 4);  // the CTA's h-th 128-row block of A
 #pragma unroll
-            for (int k = 0; k < BK / UMMA_K; ++k)
-              umma_f16_pair(d_tmem, dah + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+            for (int k = 0; k < kRowBytes / kMmaBytes; ++k)
+              umma_pair<kFp8>(d_tmem, dah + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
             if (kb == num_kb - 1) umma_commit_pair16(&s.tmem_full[slot]);
           }
           umma_commit_pair16(&s.empty[stage]);
@@ -203,6 +223,8 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     const T* bias = static_cast<const T*>(bias_v);
     [[maybe_unused]] T* out = static_cast<T*>(out_v);
     [[maybe_unused]] const T* ref = static_cast<const T*>(ref_v);
+    float alpha = 1.0f;
+    if constexpr (kFp8) alpha = __fmul_rn(__ldg(scale_a), __ldg(scale_b));
     uint32_t unit = 0;  // accumulator use counter, as in the MMA issuer
     uint32_t epi_uses = 0;       // loss mode: staging-buffer use counter (buffer = use % 2, barrier phase = (use / 2) % 2)
     float loss = 0.f;
@@ -252,7 +274,7 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                 if (col < N) {
                   float f[8];
 #pragma unroll
-                  for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
+                  for (int i = 0; i < 8; ++i) f[i] = kFp8 ? __fmul_rn(__uint_as_float(r[j + i]), alpha) : __uint_as_float(r[j + i]);
                   if (bias != nullptr) {
                     const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
                     const T* bp = reinterpret_cast<const T*>(&bv);
@@ -304,7 +326,7 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
                 const int col = n0 + c0 + 32 * h + j;
                 float f[8];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) f[i] = __uint_as_float(r[j + i]);
+                for (int i = 0; i < 8; ++i) f[i] = kFp8 ? __fmul_rn(__uint_as_float(r[j + i]), alpha) : __uint_as_float(r[j + i]);
                 if (bias != nullptr && col < N) {
                   const uint4 bv = __ldg(reinterpret_cast<const uint4*>(bias + col));
                   const T* bp = reinterpret_cast<const T*>(&bv);
@@ -363,15 +385,17 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   }
 }
 
-static bool make_map16_pair(CUtensorMap* m, const void* base, int64_t rows, int64_t K, int box_rows, bool half) {
+// operand [rows, K] row-major (K-major), boxes of `box_rows` rows x one 128-byte swizzle row; esize 2 (bf16 / f16) or 1 (E4M3)
+static bool make_map_pair(CUtensorMap* m, const void* base, int64_t rows, int64_t K, int box_rows, int esize, bool half) {
   EncodeTiledFn fn = encode_fn();
   if (fn == nullptr) { set_error("cuTensorMapEncodeTiled is not available from the driver"); return false; }
   const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
-  const cuuint64_t strides[1] = {(cuuint64_t)K * 2};
-  const cuuint32_t box[2] = {(cuuint32_t)f16p::BK, (cuuint32_t)box_rows};
+  const cuuint64_t strides[1] = {(cuuint64_t)K * (cuuint64_t)esize};
+  const cuuint32_t box[2] = {(cuuint32_t)(f16p::kRowBytes / esize), (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = fn(m, half ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                        const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+  const CUtensorMapDataType dt = esize == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                                            : (half ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+  const CUresult r = fn(m, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                         CU_TENSOR_MAP_SWIZZLE_128B, MO_LAB_L2PROMO, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed (CUresult %d)", (int)r); return false; }
   return true;
@@ -392,19 +416,22 @@ static bool make_map16_out(CUtensorMap* m, void* base, int64_t M, int64_t N, boo
   return true;
 }
 
-template <bool kHalf, bool kLoss, int kMH>
+template <bool kHalf, bool kLoss, int kMH, bool kFp8>
 static int linear_pair_launch(const void* x, const void* w, const void* bias, void* out, const void* ref,
-                              double* loss_acc, int M, int N, int K, cudaStream_t s) {
+                              double* loss_acc, const float* scale_a, const float* scale_b, int M, int N, int K,
+                              cudaStream_t s, const char* what) {
   CUtensorMap ma, mb, mo;
-  if (!make_map16_pair(&ma, x, M, K, f16p::Cfg<kMH>::BMC, kHalf) || !make_map16_pair(&mb, w, N, K, f16p::BNH, kHalf)) return MO_ERR_ARG;
+  const int esize = kFp8 ? 1 : 2;
+  if (!make_map_pair(&ma, x, M, K, f16p::Cfg<kMH>::BMC, esize, kHalf) || !make_map_pair(&mb, w, N, K, f16p::BNH, esize, kHalf))
+    return MO_ERR_ARG;
   // the [M, N] tensor the epilogue streams through its staging buffers: `out` (stored) or, in loss mode, `ref` (loaded)
   if (!make_map16_out(&mo, kLoss ? const_cast<void*>(ref) : out, M, N, kHalf)) return MO_ERR_ARG;
-  auto kern = linear_pair_kernel<kHalf, kLoss, kMH>;
+  auto kern = linear_pair_kernel<kHalf, kLoss, kMH, kFp8>;
   const int smem = (int)sizeof(f16p::Smem<kMH>) + 1024;
   static bool configured = false;
   if (!configured) {
     const cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
-    if (e != cudaSuccess) { set_error("mo_linear_pair: cudaFuncSetAttribute: %s", cudaGetErrorString(e)); return (int)e; }
+    if (e != cudaSuccess) { set_error("%s: cudaFuncSetAttribute: %s", what, cudaGetErrorString(e)); return (int)e; }
     configured = true;
   }
   constexpr int BMC = f16p::Cfg<kMH>::BMC;
@@ -414,9 +441,9 @@ static int linear_pair_launch(const void* x, const void* w, const void* bias, vo
   // here) wants small groups - B stays resident, A is read once; wider weights want more M-blocks per pass over B
   int group_m = MO_LAB_GROUPM;
   if (group_m <= 0) group_m = (N <= 4096 ? 2 : 8) * (kMH == 2 ? 1 : 2);
-  kern<<<2 * pairs, f16p::kThreadsG, smem, s>>>(ma, mb, mo, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), M, N, K,
-                                                 group_m);
-  return check_launch("mo_linear_pair");
+  kern<<<2 * pairs, f16p::kThreadsG, smem, s>>>(ma, mb, mo, bias, out, ref, loss_acc, 1.0 / ((double)M * (double)N), scale_a,
+                                                 scale_b, M, N, K, group_m);
+  return check_launch(what);
 }
 
 // Which form runs (profiles/r02_gemm_lab_mh2.txt, r02_gemm_lab_loss.txt; sustained TFLOP/s at M = 16384 on B200):
@@ -424,13 +451,14 @@ static int linear_pair_launch(const void* x, const void* w, const void* bias, vo
 //   loss : its epilogue (TMEM read + `ref` from the staging buffers + the squared error) is about twice the plain one and
 //          both accumulators of the 512 x 256 form belong to one tile, so it is only hidden by a long K loop: 512 x 256
 //          from K = 8192 (+8 % at K = 14336), 256 x 256 below (where 512 x 256 measured -4 %).
-template <bool kHalf, bool kLoss>
+template <bool kHalf, bool kLoss, bool kFp8>
 static int linear_pair_pick(const void* x, const void* w, const void* bias, void* out, const void* ref, double* loss_acc,
-                            int M, int N, int K, cudaStream_t s) {
+                            const float* scale_a, const float* scale_b, int M, int N, int K, cudaStream_t s,
+                            const char* what) {
   int mh = MO_LAB_MH;
   if (mh != 1 && mh != 2) mh = (kLoss && K < 8192) || M <= 256 ? 1 : 2;
-  return mh == 2 ? linear_pair_launch<kHalf, kLoss, 2>(x, w, bias, out, ref, loss_acc, M, N, K, s)
-                 : linear_pair_launch<kHalf, kLoss, 1>(x, w, bias, out, ref, loss_acc, M, N, K, s);
+  return mh == 2 ? linear_pair_launch<kHalf, kLoss, 2, kFp8>(x, w, bias, out, ref, loss_acc, scale_a, scale_b, M, N, K, s, what)
+                 : linear_pair_launch<kHalf, kLoss, 1, kFp8>(x, w, bias, out, ref, loss_acc, scale_a, scale_b, M, N, K, s, what);
 }
 
 }  // namespace mo
@@ -451,8 +479,30 @@ extern "C" int mo_linear_pair(const void* x, const void* w, const void* bias, vo
   const bool half = dtype == MO_F16;
   cudaStream_t s = static_cast<cudaStream_t>(stream);
   const int m = (int)M, n = (int)N, k = (int)K;
-  if (half) return loss ? linear_pair_pick<true, true>(x, w, bias, out, ref, loss_acc, m, n, k, s)
-                        : linear_pair_pick<true, false>(x, w, bias, out, ref, loss_acc, m, n, k, s);
-  return loss ? linear_pair_pick<false, true>(x, w, bias, out, ref, loss_acc, m, n, k, s)
-              : linear_pair_pick<false, false>(x, w, bias, out, ref, loss_acc, m, n, k, s);
+  const char* what = "mo_linear_pair";
+  if (half) return loss ? linear_pair_pick<true, true, false>(x, w, bias, out, ref, loss_acc, nullptr, nullptr, m, n, k, s, what)
+                        : linear_pair_pick<true, false, false>(x, w, bias, out, ref, loss_acc, nullptr, nullptr, m, n, k, s, what);
+  return loss ? linear_pair_pick<false, true, false>(x, w, bias, out, ref, loss_acc, nullptr, nullptr, m, n, k, s, what)
+              : linear_pair_pick<false, false, false>(x, w, bias, out, ref, loss_acc, nullptr, nullptr, m, n, k, s, what);
+}
+
+// FP8 per-tensor real-quant linear (the reference's `torch._scaled_mm` backend, backends/fp8_per_tensor_gemm.py:36-50) on the
+// same kernel: kind::f8f6f4, K = 32 codes per instruction, out = T(acc * (scale_a * scale_b) + bias).
+extern "C" int mo_linear_fp8_pair(const uint8_t* a, const uint8_t* b, const float* scale_a, const float* scale_b,
+                                  const void* bias, void* out, int64_t M, int64_t N, int64_t K, int out_dtype,
+                                  void* stream) {
+  if (M < 0 || N < 0 || K < 0) { set_error("mo_linear_fp8_pair: bad shape"); return MO_ERR_SHAPE; }
+  if (M == 0 || N == 0) return MO_OK;
+  if (out_dtype != MO_BF16 && out_dtype != MO_F16) { set_error("mo_linear_fp8_pair: bf16 / f16 output only"); return MO_ERR_DTYPE; }
+  if (!a || !b || !scale_a || !scale_b || !out) { set_error("mo_linear_fp8_pair: NULL pointer"); return MO_ERR_NULL; }
+  if (K < 16 || K % 16 != 0 || N % 8 != 0) { set_error("mo_linear_fp8_pair: K %% 16 and N %% 8 required"); return MO_ERR_SHAPE; }
+  if (M > INT32_MAX || N > INT32_MAX || K > INT32_MAX) { set_error("mo_linear_fp8_pair: dimension too large"); return MO_ERR_SHAPE; }
+  auto mis = [](const void* p) { return p && (reinterpret_cast<uintptr_t>(p) & 15u) != 0; };
+  if (mis(a) || mis(b) || mis(bias) || mis(out)) { set_error("mo_linear_fp8_pair: pointers must be 16-byte aligned"); return MO_ERR_ARG; }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const char* what = "mo_linear_fp8_pair";
+  const int m = (int)M, n = (int)N, k = (int)K;
+  return out_dtype == MO_F16
+             ? linear_pair_pick<true, false, true>(a, b, bias, out, nullptr, nullptr, scale_a, scale_b, m, n, k, s, what)
+             : linear_pair_pick<false, false, true>(a, b, bias, out, nullptr, nullptr, scale_a, scale_b, m, n, k, s, what);
 }

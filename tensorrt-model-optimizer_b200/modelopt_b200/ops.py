@@ -791,7 +791,7 @@ def q8_pack(x, scales, kind):
     return q
 
 
-# rows from which linear_fp8 runs on CTA pairs (csrc/gemm_fp8_2cta.cu): bit-identical, 1-7 % faster on the timed shapes
+# rows from which linear_fp8 runs on CTA pairs (csrc/gemm_2cta.cu, the kernel of the bf16 pairs with kind::f8f6f4): bit-identical, 1-7 % faster on the timed shapes
 FP8_PAIR = {"min_rows": 512}
 
 

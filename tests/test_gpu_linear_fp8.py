@@ -122,7 +122,7 @@ def test_gemm_registry_dispatch():
 
 @pytest.mark.parametrize("M,N,K", [(256, 256, 128), (300, 264, 144), (1, 8, 16), (1024, 512, 1024), (4096, 4096, 4096)])
 def test_cta_pair_kernel_equals_single_cta(M, N, K):
-    """csrc/gemm_fp8_2cta.cu (cta_group::2) == csrc/gemm_fp8.cu bit for bit."""
+    """mo_linear_fp8_pair (csrc/gemm_2cta.cu with kind::f8f6f4, cta_group::2) == csrc/gemm_fp8.cu bit for bit."""
     x, w, sa, sb = _operands(M, N, K)
     a, b = ops.q8_pack(x, sa, "fp8_sat"), ops.q8_pack(w, sb, "fp8_sat")
     bv = (torch.randn(N, device="cuda") * 0.1).to(torch.bfloat16)

@@ -49,6 +49,7 @@ def run():
             continue
         lib = C.CDLL(path)
         lib.mo_linear_pair.argtypes = [C.c_void_p] * 4 + [C.c_int64] * 3 + [C.c_int] + [C.c_void_p] * 3
+        lib.mo_linear_fp8_pair.argtypes = [C.c_void_p] * 6 + [C.c_int64] * 3 + [C.c_int, C.c_void_p]
         libs[name] = lib
     for N, K in shapes:
         x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
@@ -58,11 +59,20 @@ def run():
         stream = torch.cuda.current_stream().cuda_stream
         cands = {"cublas": lambda: torch.nn.functional.linear(x, w)}
         loss_mode = os.environ.get("LAB_LOSS", "0") == "1"
+        fp8 = os.environ.get("LAB_FP8", "0") == "1"
+        if fp8:
+            a8, b8 = x.to(torch.float8_e4m3fn), w.to(torch.float8_e4m3fn)
+            one = torch.ones(1, device="cuda")
+            flops = 2.0 * M * N * K
+            cands = {"scaled_mm": lambda: torch._scaled_mm(a8, b8.t(), one, one, None, out_dtype=torch.bfloat16, use_fast_accum=True)}
         ref = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
         acc = torch.zeros(1, dtype=torch.float64, device="cuda")
         for name, lib in libs.items():
             def fn(lib=lib):
-                if loss_mode:
+                if fp8:
+                    rc = lib.mo_linear_fp8_pair(a8.data_ptr(), b8.data_ptr(), one.data_ptr(), one.data_ptr(), None, out.data_ptr(),
+                                                M, N, K, 2, stream)
+                elif loss_mode:
                     rc = lib.mo_linear_pair(x.data_ptr(), w.data_ptr(), None, None, M, N, K, 2, ref.data_ptr(), acc.data_ptr(), stream)
                 else:
                     rc = lib.mo_linear_pair(x.data_ptr(), w.data_ptr(), None, out.data_ptr(), M, N, K, 2, None, None, stream)

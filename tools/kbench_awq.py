@@ -110,5 +110,16 @@ def main():
         print(f"weight block amax: max rel diff {((a - b).abs() / b.abs().clamp_min(1e-30)).max().item():.3e}, identical {(a == b).float().mean().item() * 100:.1f}%")
 
 
+def with_clocks(fn):
+    """Run fn() with the SM clock and throttle reasons sampled (bench.py's sampler) and print them: a kernel figure without
+    the clocks it was taken at is a claim, not a measurement."""
+    sys.path[:0] = [ROOT]
+    from bench import Clocks
+
+    with Clocks(torch.cuda.current_device()) as clk:
+        fn()
+    print("# clocks during this run:", clk.summary(), flush=True)
+
+
 if __name__ == "__main__":
-    main()
+    with_clocks(main)
