@@ -26,7 +26,8 @@ from ..calib import MaxCalibrator
 from ..config import QuantizerAttributeConfig
 from .tensor_quantizer import SequentialQuantizer, TensorQuantizer
 
-__all__ = ["QuantModule", "QuantInputBase", "QuantLinearConvBase", "QuantModuleRegistry", "ParallelState"]
+__all__ = ["QuantModule", "QuantInputBase", "QuantLinearConvBase", "QuantModuleRegistry", "ParallelState",
+           "RealQuantLinear"]
 
 QUANT_DESC_8BIT_PER_TENSOR = QuantizerAttributeConfig(num_bits=8)
 QUANT_DESC_8BIT_LINEAR_WEIGHT_PER_ROW = QuantizerAttributeConfig(num_bits=8, axis=(0,))
@@ -449,6 +450,29 @@ class _QuantLinear(QuantLinearConvBase):
                 out = ops.plain_linear(q(input), self.quantized_weight(), self.bias)
             return self.output_quantizer(out)
         return super().forward(input, *args, **kwargs)
+
+
+class RealQuantLinear(_QuantLinear):
+    """quant_linear.py:196-244 under its own name.  In this package one class serves both roles — `_QuantLinear` runs the
+    fake-quant linear, and with `real_quant_gemm` on (or a packed `QTensorWrapper` weight from `mtq.compress`) the
+    real-quant one — so this is that class plus the reference's attribute names."""
+
+    list_of_scale_tensors = ["_scale", "_double_scale", "_scale_zeros"]
+    allow_real_quant_gemm = True
+
+    @property
+    def _should_run_real_quant_gemm(self):
+        return super()._should_run_real_quant_gemm and self.allow_real_quant_gemm
+
+    def has_real_quant_gemm_impl(self, input, *args, **kwargs) -> bool:
+        """quant_linear.py:211-221: the registry's match for this call, cached on the module."""
+        if "_real_quant_gemm_impl" not in self.__dict__:
+            from ..backends import gemm_registry
+
+            self.__dict__["_real_quant_gemm_impl"] = gemm_registry.find_match(self, input, *args, **kwargs)
+            if self.__dict__["_real_quant_gemm_impl"] is None:
+                warnings.warn(f"RealQuantLinear: No real-quant GEMM found: {self}.")
+        return self.__dict__["_real_quant_gemm_impl"] is not None
 
 
 class _QuantConv(QuantLinearConvBase):
