@@ -41,13 +41,26 @@ def replace_quant_module(model: nn.Module, registry=QuantModuleRegistry):
     return model
 
 
-def _match(pattern: str | Callable, name: str, module, parent_class, model, parents=None) -> bool:
+_PATTERN_CACHE: dict = {}
+
+
+def _compiled(pattern: str):
+    rx = _PATTERN_CACHE.get(pattern)
+    if rx is None:
+        rx = _PATTERN_CACHE[pattern] = re.compile(fnmatch.translate(pattern))
+    return rx
+
+
+def _match(pattern: str | Callable, name: str, module, parent_class, model, parents=None, norm=None) -> bool:
     if not isinstance(module, (TensorQuantizer, SequentialQuantizer)):
         return False
     if isinstance(pattern, str):
-        norm = _EXPERT_LIST_RE.sub(lambda m: m.group(1).removesuffix("s"), name)
-        if not (fnmatch.fnmatch(name, pattern) or (norm != name and fnmatch.fnmatch(norm, pattern))):
-            return False
+        rx = _compiled(pattern)  # fnmatch semantics (case-sensitive on POSIX), compiled once per pattern
+        if rx.match(name) is None:
+            if norm is None:
+                norm = _EXPERT_LIST_RE.sub(lambda m: m.group(1).removesuffix("s"), name)
+            if norm == name or rx.match(norm) is None:
+                return False
     elif callable(pattern):
         if not pattern(name):
             return False
@@ -69,12 +82,14 @@ class _QuantizerIndex:
         self.model = model
         self.parents = dict(model.named_modules())
         self.items = [(n, m) for n, m in self.parents.items() if isinstance(m, (TensorQuantizer, SequentialQuantizer))]
+        # expert-list names ("weight_quantizers.3" -> "weight_quantizer") normalised once, not once per config entry
+        self.norm = {n: _EXPERT_LIST_RE.sub(lambda m: m.group(1).removesuffix("s"), n) for n, _ in self.items}
 
     def replace(self, name, module):
         parent = self.parents[name.rpartition(".")[0]]
         setattr(parent, name.rpartition(".")[2], module)
         fresh = _QuantizerIndex(self.model)  # the children of the old / new object changed too; rare, so just re-list
-        self.parents, self.items = fresh.parents, fresh.items
+        self.parents, self.items, self.norm = fresh.parents, fresh.items, fresh.norm
 
 
 def set_quantizer_attributes_full(model, pattern, attributes, parent_class=None, _index=None):
@@ -84,7 +99,7 @@ def set_quantizer_attributes_full(model, pattern, attributes, parent_class=None,
         raise ValueError(f"Invalid type for attributes: {type(attributes)}")
     idx = _index if _index is not None else _QuantizerIndex(model)
     for name, module in list(idx.items):  # snapshot: quantizers created by a replacement below are not visited
-        if idx.parents.get(name) is not module or not _match(pattern, name, module, parent_class, model, idx.parents):
+        if idx.parents.get(name) is not module or not _match(pattern, name, module, parent_class, model, idx.parents, idx.norm.get(name)):
             continue
         if isinstance(attributes, list):
             if not isinstance(module, SequentialQuantizer) or len(module) != len(attributes):
@@ -102,7 +117,7 @@ def set_quantizer_attributes_partial(model, pattern, attributes: dict[str, Any],
     """Update only the given attributes of the matched quantizers."""
     idx = _index if _index is not None else _QuantizerIndex(model)
     for name, module in idx.items:
-        if _match(pattern, name, module, parent_class, model, idx.parents):
+        if _match(pattern, name, module, parent_class, model, idx.parents, idx.norm.get(name)):
             targets = module if isinstance(module, SequentialQuantizer) else [module]
             for q in targets:
                 q.set_from_attribute_config(attributes)

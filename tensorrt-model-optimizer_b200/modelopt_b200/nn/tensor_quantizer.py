@@ -75,6 +75,60 @@ def _standardize_constructor_args(val):
     return cls, args, kwargs
 
 
+def _set_calibrator(q, val):
+    if val in ("max", "histogram"):
+        cls = calib.MaxCalibrator if val == "max" else calib.HistogramCalibrator
+        args, kwargs = (q._num_bits, q._axis, q._unsigned), {}
+    else:
+        cls, args, kwargs = _standardize_constructor_args(val)
+    return cls(*args, **kwargs)
+
+
+def _set_axis(q, val):
+    if getattr(q, "_calibrator", None) is not None:
+        q._calibrator._axis = val
+    return val
+
+
+def _set_block_sizes(q, val):
+    if val is not None:
+        q._axis = None
+        if getattr(q, "_calibrator", None) is not None:
+            q._calibrator._axis = None
+    return val
+
+
+def _set_constant_amax(q, val):
+    if val is not None:
+        q.amax = float(val)
+    return val
+
+
+def _unsupported(name):
+    def f(q, val):
+        if val:
+            raise NotImplementedError(f"modelopt_b200: quantizer attribute '{name}' is not implemented "
+                                      "(outside the hot path, SURVEY.md section 8)")
+        return val
+    return f
+
+
+# config field -> (attribute name, setter(quantizer, value)); every other field `x` is stored as `_x`
+_ATTRIBUTE_SETTERS: dict = {
+    "enable": ("_disabled", lambda q, v: v is False),
+    "type": ("_dynamic", lambda q, v: v == "dynamic"),
+    "calibrator": ("_calibrator", _set_calibrator),
+    "axis": ("_axis", _set_axis),
+    "block_sizes": ("_block_sizes", _set_block_sizes),
+    "backend": ("backend", lambda q, v: v),
+    "backend_extra_args": ("backend_extra_args", lambda q, v: v or {}),
+    "use_constant_amax": ("_use_constant_amax", lambda q, v: v),
+    "constant_amax": ("_constant_amax", _set_constant_amax),
+    "bias": ("_bias", _unsupported("bias")),
+    "rotate": ("_rotate", _unsupported("rotate")),
+}
+
+
 class TensorQuantizer(nn.Module):
     """Quantizes (fake or real) or calibrates its input, depending on ``_if_quant`` / ``_if_calib``."""
 
@@ -86,74 +140,32 @@ class TensorQuantizer(nn.Module):
         cfg = quant_attribute_cfg if quant_attribute_cfg is not None else QuantizerAttributeConfig()
         if amax is not None:
             self.amax = amax
-        self._use_constant_amax = False
-        self._constant_amax = None
+        put = object.__setattr__  # plain Python values: no need for nn.Module.__setattr__'s Parameter / Module checks
+        put(self, "_use_constant_amax", False)
+        put(self, "_constant_amax", None)
         self.set_from_attribute_config(cfg)
-        self._if_quant = if_quant
-        self._if_calib = if_calib
-        self._enable_pre_quant_scale = True
-        self._dequantize = False
-        self._input_dtype = None
-        self._bias_calibrator = None
-        self._quantizer_cache = None
+        put(self, "_if_quant", if_quant)
+        put(self, "_if_calib", if_calib)
+        put(self, "_enable_pre_quant_scale", True)
+        put(self, "_dequantize", False)
+        put(self, "_input_dtype", None)
+        put(self, "_bias_calibrator", None)
+        put(self, "_quantizer_cache", None)
 
     # ------------------------------------------------------------------ configuration
     def set_from_attribute_config(self, attribute_cfg):
         """tensor_quantizer.py:228-289."""
-
-        def calibrator_setter(val):
-            if val in ("max", "histogram"):
-                cls = calib.MaxCalibrator if val == "max" else calib.HistogramCalibrator
-                args, kwargs = (self._num_bits, self._axis, self._unsigned), {}
-            else:
-                cls, args, kwargs = _standardize_constructor_args(val)
-            return cls(*args, **kwargs)
-
-        def axis_setter(val):
-            if getattr(self, "_calibrator", None) is not None:
-                self._calibrator._axis = val
-            return val
-
-        def block_sizes_setter(val):
-            if val is not None:
-                self._axis = None
-                if getattr(self, "_calibrator", None) is not None:
-                    self._calibrator._axis = None
-            return val
-
-        def constant_amax_setter(val):
-            if val is not None:
-                self.amax = float(val)
-            return val
-
-        def unsupported(name):
-            def f(val):
-                if val:
-                    raise NotImplementedError(f"modelopt_b200: quantizer attribute '{name}' is not implemented "
-                                              "(outside the hot path, SURVEY.md section 8)")
-                return val
-            return f
-
-        custom: dict[str, tuple[str, Callable]] = {
-            "enable": ("_disabled", lambda v: v is False),
-            "type": ("_dynamic", lambda v: v == "dynamic"),
-            "calibrator": ("_calibrator", calibrator_setter),
-            "axis": ("_axis", axis_setter),
-            "block_sizes": ("_block_sizes", block_sizes_setter),
-            "backend": ("backend", lambda v: v),
-            "backend_extra_args": ("backend_extra_args", lambda v: v or {}),
-            "use_constant_amax": ("_use_constant_amax", lambda v: v),
-            "constant_amax": ("_constant_amax", constant_amax_setter),
-            "bias": ("_bias", unsupported("bias")),
-            "rotate": ("_rotate", unsupported("rotate")),
-        }
+        fields = QuantizerAttributeConfig.model_fields
+        setattr_ = object.__setattr__
         for attribute, val in attribute_cfg.items():
-            assert attribute in QuantizerAttributeConfig.model_fields, (
-                f"{attribute} is not a valid `TensorQuantizer` attribute")
-            name, setter = custom.get(attribute, (f"_{attribute}", lambda v: v))
+            assert attribute in fields, f"{attribute} is not a valid `TensorQuantizer` attribute"
+            entry = _ATTRIBUTE_SETTERS.get(attribute)
             # plain Python values (never a Parameter / Module / buffer): skip nn.Module.__setattr__'s type checks, which
             # dominate quantizer construction and set_quantizer_by_cfg on a 676-quantizer model (properties still apply)
-            object.__setattr__(self, name, setter(val))
+            if entry is None:
+                setattr_(self, "_" + attribute, val)
+            else:
+                setattr_(self, entry[0], entry[1](self, val))
         if self.is_mx_format:
             self._pass_through_bwd = True  # tensor_quantizer.py:289-290
 
