@@ -311,6 +311,13 @@ int mo_linear_qdq(const void* x, const void* w, const void* bias, void* out, int
 int mo_linear_nvfp4(const void* a_codes, const void* a_sf, const float* a_gs, const void* b_codes, const void* b_sf,
                     const float* b_gs, const void* bias, void* out, int64_t M, int64_t N, int64_t K, int out_dtype,
                     void* stream);
+/* The same product (same operands, same results) on CTA pairs: tcgen05 cta_group::2, 256 x 256 pair tile, each CTA holds
+ * half of the B tile (the single-CTA kernel is bound by shared-memory bandwidth), scale factors carried into tensor
+ * memory by dedicated warps, overlapped accumulators, TMA-store epilogue.  Same reference role as mo_linear_nvfp4
+ * (backends/nvfp4_gemm.py:28-125). */
+int mo_linear_nvfp4_pair(const void* a_codes, const void* a_sf, const float* a_gs, const void* b_codes, const void* b_sf,
+                         const float* b_gs, const void* bias, void* out, int64_t M, int64_t N, int64_t K, int out_dtype,
+                         void* stream);
 /* E4M3 block scales [rows, kblocks] row-major (mo_nvfp4_pack's sf_out) -> the 128-row x 4-block tile order of
  * tcgen05 scale factors, rows zero-padded to a multiple of row_pad (128 or 256), kblocks to a multiple of 4. */
 int64_t mo_nvfp4_sf_swizzle_bytes(int64_t rows, int64_t kblocks, int row_pad);

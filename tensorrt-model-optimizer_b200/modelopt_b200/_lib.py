@@ -60,6 +60,7 @@ SIGNATURES = {
     "mo_linear_pair": [_p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p, _p],
     "mo_linear_qdq": [_p, _p, _p, _p, _i64, _i64, _i64, _i, _p, _p, _i, _i, _i, _i, _p],
     "mo_linear_nvfp4": [_p, _p, _p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p],
+    "mo_linear_nvfp4_pair": [_p, _p, _p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i, _p],
     "mo_nvfp4_pack_gemm": [_p, _i64, _i64, _i, _p, _p, _p, _p],
     "mo_nvfp4_sf_swizzle_bytes": [_i64, _i64, _i],
     "mo_nvfp4_sf_swizzle": [_p, _i64, _i64, _i, _p, _p],

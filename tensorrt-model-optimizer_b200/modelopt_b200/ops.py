@@ -1227,9 +1227,15 @@ def nvfp4_quantize_operand(x, global_amax, row_pad):
     return codes, sfw, gs
 
 
-def linear_nvfp4(a_codes, a_sf, a_gs, b_codes, b_sf, b_gs, bias=None, out_dtype=torch.bfloat16, out=None):
+# Which NVFP4 GEMM runs: "auto" = the CTA-pair kernel (256 x 256 pair tile) when there are more than 128 rows, the single-CTA
+# kernel (128 x 256) otherwise; "pair" / "single" force one (MODELOPT_B200_NVFP4_GEMM).
+NVFP4_GEMM = {"form": os.environ.get("MODELOPT_B200_NVFP4_GEMM", "auto")}
+
+
+def linear_nvfp4(a_codes, a_sf, a_gs, b_codes, b_sf, b_gs, bias=None, out_dtype=torch.bfloat16, out=None, pair=None):
     """out = (deq(a) @ deq(b)^T) + bias from packed NVFP4 operands (see nvfp4_quantize_operand), fp32 accumulation on
-    tcgen05.mma.kind::mxf4nvf4.block_scale."""
+    tcgen05.mma.kind::mxf4nvf4.block_scale.  pair: None = NVFP4_GEMM's choice, True / False = force the CTA-pair /
+    single-CTA kernel (same results)."""
     _cuda(a_codes, "linear_nvfp4")
     a2 = a_codes.contiguous().reshape(-1, a_codes.shape[-1])
     b2 = b_codes.contiguous()
@@ -1246,8 +1252,12 @@ def linear_nvfp4(a_codes, a_sf, a_gs, b_codes, b_sf, b_gs, bias=None, out_dtype=
         raise ValueError("linear_nvfp4: bias must have the output dtype and N elements")
     y = torch.empty(*a_codes.shape[:-1], N, dtype=out_dtype, device=a_codes.device) if out is None else out
     code = _DT[out_dtype]
+    if pair is None:
+        form = NVFP4_GEMM["form"]
+        pair = form == "pair" or (form == "auto" and M > 128)
+    name = "mo_linear_nvfp4_pair" if pair else "mo_linear_nvfp4"
     with _dev(a_codes):
-        _launched(lib.mo_linear_nvfp4(a2.data_ptr(), a_sf.data_ptr(), a_gs.data_ptr(), b2.data_ptr(), b_sf.data_ptr(),
-                                      b_gs.data_ptr(), b.data_ptr() if b is not None else None, y.data_ptr(), M, N, K,
-                                      code, _stream(a_codes)), "mo_linear_nvfp4")
+        _launched(getattr(lib, name)(a2.data_ptr(), a_sf.data_ptr(), a_gs.data_ptr(), b2.data_ptr(), b_sf.data_ptr(),
+                                     b_gs.data_ptr(), b.data_ptr() if b is not None else None, y.data_ptr(), M, N, K,
+                                     code, _stream(a_codes)), name)
     return y

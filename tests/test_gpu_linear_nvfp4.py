@@ -36,9 +36,40 @@ def test_nvfp4_linear_vs_cpu_oracle(M, N, K, dt):
     with ops.numerics("cpu"):
         xc, xs, xg = ops.nvfp4_quantize_operand(x.cuda(), ax.cuda(), 128)
         wc, ws, wg = ops.nvfp4_quantize_operand(w.cuda(), aw.cuda(), 256)
-    y = ops.linear_nvfp4(xc, xs, xg, wc, ws, wg, b.cuda(), out_dtype=dt).cpu().double()
     tol = (2.0 ** -7 if dt == torch.bfloat16 else 2.0 ** -10) * want.abs().max().item()
-    assert (y - want).abs().max().item() <= tol
+    ys = {}
+    for pair in (False, True):      # single-CTA kernel (128 x 256 tile) and CTA-pair kernel (256 x 256 pair tile)
+        ys[pair] = ops.linear_nvfp4(xc, xs, xg, wc, ws, wg, b.cuda(), out_dtype=dt, pair=pair)
+        assert (ys[pair].cpu().double() - want).abs().max().item() <= tol
+    # exact products, the same K order, fp32 accumulation in tensor memory: the two kernels agree bit for bit
+    assert torch.equal(ys[False], ys[True])
+
+
+@pytest.mark.parametrize("M,N,K", [(1024, 1536, 1280), (2049, 520, 768), (4096, 4096, 4096)])
+def test_nvfp4_pair_kernel_many_tiles(M, N, K):
+    """More tiles than CTA pairs / several tiles per pair (accumulators alternate between the two overlapping TMEM
+    regions, scale slots and the smem ring wrap many times): pair kernel == single-CTA kernel bit for bit, twice in a row,
+    with the single-accumulator form (MO_LAB_F4P=1) agreeing as well."""
+    import os
+
+    from modelopt_b200 import ops
+
+    torch.manual_seed(K)
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16) * 2
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) * 0.05
+    b = torch.randn(N, device="cuda", dtype=torch.bfloat16)
+    a = ops.nvfp4_quantize_operand(x, x.float().abs().max(), 128)
+    bb = ops.nvfp4_quantize_operand(w, w.float().abs().max(), 256)
+    ref = ops.linear_nvfp4(*a, *bb, b, pair=False)
+    y1 = ops.linear_nvfp4(*a, *bb, b, pair=True)
+    y2 = ops.linear_nvfp4(*a, *bb, b, pair=True)
+    os.environ["MO_LAB_F4P"] = "1"
+    try:
+        y3 = ops.linear_nvfp4(*a, *bb, b, pair=True)
+    finally:
+        os.environ["MO_LAB_F4P"] = "0"
+    assert torch.equal(ref, y1) and torch.equal(y1, y2) and torch.equal(y1, y3)
+    assert ops.NVFP4_GEMM["form"] == "auto"     # more than 128 rows: the pair kernel is what linear_nvfp4 picks
 
 
 def test_nvfp4_linear_close_to_fake_quant_linear():

@@ -82,6 +82,38 @@ class Feeder:
                 del logits
 
 
+class CollectiveLog:
+    """Counts the torch.distributed.all_reduce calls the product issues inside a `with` block (op, calls, bytes): the
+    evidence that the data-parallel exchanges (amax MAX, histogram MAX / SUM) ran over the process group."""
+
+    def __init__(self):
+        self.ops = {}
+
+    def __enter__(self):
+        import torch.distributed as dist
+
+        self._dist, self._orig = dist, dist.all_reduce
+
+        def logged(tensor, op=dist.ReduceOp.SUM, *a, **k):
+            name = str(op).split(".")[-1].upper()
+            e = self.ops.setdefault(name, {"calls": 0, "bytes": 0})
+            e["calls"] += 1
+            e["bytes"] += tensor.numel() * tensor.element_size()
+            return self._orig(tensor, op, *a, **k)
+
+        dist.all_reduce = logged
+        return self
+
+    def __exit__(self, *exc):
+        self._dist.all_reduce = self._orig
+
+    def summary(self, world):
+        dist = self._dist
+        on = dist.is_available() and dist.is_initialized()
+        return {"backend": dist.get_backend() if on else None, "world_size": dist.get_world_size() if on else world,
+                "all_reduce": self.ops}
+
+
 def _timed(fn, device, dist_world):
     """Device time (CUDA events on the current stream) and wall time of fn(), both max over ranks; barrier + sync
     on both sides."""
@@ -262,10 +294,20 @@ def run(model_name="8b", presets=("nvfp4",), n_seq_total=512, micro_batch=8, seq
                 feeder.loop(model)
                 model_calib.finish_stats_collection(model, method="entropy")
 
-            _, quant_s, quant_wall = _timed(hist_calibrate, device, world)
+            with CollectiveLog() as clog:
+                _, quant_s, quant_wall = _timed(hist_calibrate, device, world)
         else:
             cfg = getattr(qcfg, PRESETS[preset])
-            _, quant_s, quant_wall = _timed(lambda: mtq.quantize(model, cfg, feeder.loop), device, world)
+            with CollectiveLog() as clog:
+                _, quant_s, quant_wall = _timed(lambda: mtq.quantize(model, cfg, feeder.loop), device, world)
+        collectives = clog.summary(world)
+        # _timed's own max-over-ranks reduction of the two clocks is not the product's
+        if world > 1 and "MAX" in collectives["all_reduce"]:
+            e = collectives["all_reduce"]["MAX"]
+            e["calls"] -= 1
+            e["bytes"] -= 16
+            if e["calls"] == 0:
+                del collectives["all_reduce"]["MAX"]
         launches = ops.LAUNCHES[0] - launches0
         h2d, d2h = feeder.h2d, feeder.d2h
         quantizers = [m for m in model.modules() if isinstance(m, TensorQuantizer)]
@@ -312,6 +354,7 @@ def run(model_name="8b", presets=("nvfp4",), n_seq_total=512, micro_batch=8, seq
             "peak_mem_gb": peak_mem / 1e9,
             "build_s": build_s,
             "n_gpus": world,
+            "collectives_in_quantize": collectives,
             "scaling": "strong",
             "plain_gemm_backend": ops.PLAIN_GEMM["backend"],
         }
