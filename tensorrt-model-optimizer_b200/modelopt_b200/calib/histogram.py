@@ -107,7 +107,9 @@ class HistogramCalibrator(_Calibrator):
         self._snap_valid = False
         self._n_collect = getattr(self, "_n_collect", 0) + 1
         # asynchronous read-back (64 bytes), looked at by a later collect: after the first batches, then every 8th
-        if self._pending is None and (self._n_collect <= 2 or self._n_collect % 8 == 0):
+        # (not while the stream is being captured into a CUDA graph: the collect itself is capturable, the read-back is not)
+        if self._pending is None and (self._n_collect <= 2 or self._n_collect % 8 == 0) \
+                and not torch.cuda.is_current_stream_capturing():
             if self._host is None:
                 self._host = torch.empty(_STATE_WORDS, dtype=torch.int32).pin_memory()
             self._host.copy_(self._state, non_blocking=True)
@@ -119,7 +121,9 @@ class HistogramCalibrator(_Calibrator):
         return max(self._init_bins, self._snap[_NBINS] if self._snap else 0)
 
     def _poll(self):
-        if self._pending is not None and self._pending.query():
+        if self._pending is None or torch.cuda.is_current_stream_capturing():
+            return
+        if self._pending.query():
             self._snap = self._host.tolist()
             self._pending = None
             self._raise_if_frozen(self._snap)

@@ -149,3 +149,30 @@ def test_whole_equals_chunked_and_single_bin_extremes(dt, skip_zeros, nbins):
     c.zero_()
     ops.hist_into(o, torch.ones(1, device="cuda"), c)
     assert int(c[-1]) == 1 << 21 and int(c[:-1].sum()) == 0
+
+
+def test_collect_is_capturable_in_a_cuda_graph(calib):
+    """The sync-free collect enqueues kernels only (its asynchronous state read-back is skipped while the stream is being
+    captured), so a captured collect - including a batch that grows the range - replays to the counts of the eager path."""
+    torch.manual_seed(5)
+    x0 = torch.randn(64, 1024, device="cuda", dtype=torch.bfloat16)
+    xs = [torch.randn(64, 1024, device="cuda", dtype=torch.bfloat16) * s for s in (0.5, 3.0, 1.0)]   # the second one grows
+    eager, graphed = calib.HistogramCalibrator(8, None, False), calib.HistogramCalibrator(8, None, False)
+    eager.collect(x0)
+    graphed.collect(x0)
+    for x in xs:
+        eager.collect(x)
+    torch.cuda.synchronize()
+    s = torch.cuda.Stream()
+    with torch.cuda.stream(s):
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=s):
+            for x in xs:
+                graphed.collect(x)
+        g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(eager._calib_hist, graphed._calib_hist)
+    assert torch.equal(eager._calib_bin_edges, graphed._calib_bin_edges)
+    graphed.collect(xs[0])          # and the calibrator keeps working eagerly afterwards (read-back included)
+    eager.collect(xs[0])
+    assert torch.equal(eager._calib_hist, graphed._calib_hist)
