@@ -44,6 +44,10 @@ constexpr int kMmaBytes = 32;                 // K bytes per tcgen05.mma (16 x 1
 #ifndef MO_LAB_L2PROMO
 #define MO_LAB_L2PROMO CU_TENSOR_MAP_L2_PROMOTION_L2_256B
 #endif
+#ifndef MO_LAB_PROLOGUE
+#define MO_LAB_PROLOGUE 4
+#endif
+constexpr int kPrologue = MO_LAB_PROLOGUE;    // 512 x 256 form: K steps per tile issued accumulator-major (see the MMA issuer)
 constexpr int kEpiCols = 64;                  // columns per staged chunk: 64 bf16 = one 128-byte swizzle row
 constexpr uint32_t kEpiBytes = 32 * kEpiCols * 2;  // one warp's chunk: 32 rows x 128 bytes
 constexpr int kThreadsG = 192;
@@ -193,7 +197,38 @@ linear_pair_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       int stage = 0;
       uint32_t phase = 0, unit = 0;  // unit = accumulator use counter: slot = unit % 2, its barrier phase = (unit / 2) % 2
       for (int tile = pair; tile < num_tiles; tile += num_pairs) {
-        for (int kb = 0; kb < num_kb; ++kb) {
+        int kb0 = 0;
+        if constexpr (kMH == 2 && kPrologue > 0) {
+          // Both accumulators belong to this tile and the previous tile's epilogue drains them one after the other, so the
+          // second one is free ~2000 clocks after the first.  The tile's first kPrologue K steps are therefore issued
+          // accumulator-major: all of them for half 0, then for half 1 (their stages are released on the second pass) -
+          // the second accumulator's drain hides behind the first half's MMAs instead of stalling the pipe.
+          const int pro = min(kPrologue, num_kb);
+#pragma unroll 1
+          for (int h = 0; h < 2; ++h) {
+            const uint32_t u = unit + (uint32_t)h, slot = u & 1u;
+            mbar_wait(&s.tmem_empty[slot], ((u >> 1) & 1u) ^ 1u);
+            tc_fence_after();
+            const uint32_t d_tmem = tmem + slot * (uint32_t)BN;
+            int st = stage;
+            uint32_t ph = phase;
+            for (int kb = 0; kb < pro; ++kb) {
+              mbar_wait(&s.full[st], ph);
+              tc_fence_after();
+              const uint64_t dah = umma_desc(smem_u32(s.a[st])) + (uint64_t)((h * BM * kRowBytes) >> 4);
+              const uint64_t db = umma_desc(smem_u32(s.b[st]));
+#pragma unroll
+              for (int k = 0; k < kRowBytes / kMmaBytes; ++k)
+                umma_pair<kFp8>(d_tmem, dah + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+              if (kb == num_kb - 1) umma_commit_pair16(&s.tmem_full[slot]);
+              if (h == 1) umma_commit_pair16(&s.empty[st]);
+              if (++st == kStages) { st = 0; ph ^= 1; }
+            }
+            if (h == 1) { stage = st; phase = ph; }
+          }
+          kb0 = pro;
+        }
+        for (int kb = kb0; kb < num_kb; ++kb) {
           mbar_wait(&s.full[stage], phase);
           tc_fence_after();
           const uint64_t da = umma_desc(smem_u32(s.a[stage])), db = umma_desc(smem_u32(s.b[stage]));
