@@ -248,6 +248,8 @@ def sync_histograms(model: nn.Module, group=None):
     cals = [m._calibrator for m in model.modules()
             if isinstance(m, TensorQuantizer) and isinstance(getattr(m, "_calibrator", None), HistogramCalibrator)
             and m._calibrator._state is not None and not m._calibrator._synced]
+    for c in cals:
+        c._join()  # the last collect's decision may still be running on the calibrators' side stream
     n_cals = torch.tensor([len(cals)], dtype=torch.int64, device=cals[0]._state.device if cals else None)
     if cals:
         lo, hi = n_cals.clone(), n_cals.clone()
