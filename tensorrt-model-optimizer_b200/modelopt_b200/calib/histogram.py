@@ -29,6 +29,7 @@ amax up in the edge array exactly like the reference.  ``method="mse"`` reproduc
 
 from __future__ import annotations
 
+import os
 import warnings
 
 import torch
@@ -43,18 +44,6 @@ __all__ = ["HistogramCalibrator", "calibrate_weights"]
 _NBINS, _RANGE_MAX, _WIDTH, _LAST_END, _FLAGS, _FIRST_AMAX, _BATCH_AMAX = 0, 1, 2, 3, 4, 5, 6
 _STATE_WORDS = 16
 _FLAG_OVERFLOW, _FLAG_NONFINITE = 1, 2
-
-
-_SIDE_STREAMS = {}
-
-
-def _side_stream(device):
-    """One extra stream per device for the data-parallel exchange of every HistogramCalibrator on it."""
-    key = (device.type, device.index if device.index is not None else torch.cuda.current_device())
-    st = _SIDE_STREAMS.get(key)
-    if st is None:
-        st = _SIDE_STREAMS[key] = torch.cuda.Stream(device=device)
-    return st
 
 
 class HistogramCalibrator(_Calibrator):
@@ -76,6 +65,9 @@ class HistogramCalibrator(_Calibrator):
         self._torch_hist = torch_hist
         # data-parallel group whose ranks calibrate together: False = none; None = the default (world) group
         self.dp_group = False
+        # "finish": ranks agree on the bin width at the first batch and merge at the end; "step": they exchange the batch
+        # maximum on every collect (see collect)
+        self.dp_sync = os.environ.get("MODELOPT_B200_HIST_DP_SYNC", "finish")
         # "cpu": build grown bin edges with torch.arange on the CPU (what the reference computes for CPU tensors;
         # CPU arange evaluates start + i*step in fp64, CUDA arange in fp32, so edges can differ in the last bit)
         self.numerics = None
@@ -105,34 +97,27 @@ class HistogramCalibrator(_Calibrator):
             self._buf = torch.zeros(self._init_bins * self._headroom, dtype=torch.int64, device=x.device)
             self._snap = None
         else:
-            self._join()  # the previous batch's decision (taken on the side stream in data-parallel runs) precedes this one
             self._poll()  # a finished read-back of an earlier batch: learn the bin count, report a frozen state
         hint = self._hint()
         self._synced = False
         self._edges_cache = None
         self._snap_valid = False
         self._n_collect = getattr(self, "_n_collect", 0) + 1
-        if self._group_size() > 1:
-            # Data-parallel: the batch maximum is all-reduced(MAX) (one word) so that every rank takes the same grow /
-            # no-grow decision.  The binning pass runs on the caller's stream under the CURRENT range; the exchange and
-            # what depends on it (decision, the rare re-binning pass, the state read-back) run on a side stream, so the
-            # model's next kernels do not wait for the collective's latency - with one blocking all-reduce per collect
-            # (224 per Llama-8B forward) eight ranks spent 3x the single-GPU histogram overhead waiting for each other.
+        if self._group_size() > 1 and (first or self.dp_sync == "step"):
+            # Data-parallel.  The FIRST batch's maximum is all-reduced(MAX): it fixes the bin width, which must be the same on
+            # every rank for the counts to be summable at the end.  dp_sync == "finish" (default): later batches are collected
+            # locally - each rank grows its own range in units of the common width - and `sync_histograms` merges the ranks
+            # at the end (MAX of the ranges, SUM of the counts): no collective on the per-batch path.  dp_sync == "step": the
+            # batch maximum is exchanged on EVERY collect, so all ranks take the same grow / no-grow decision and the result is
+            # bit-identical to one process fed the union of the ranks' batches step by step - at one blocking one-word
+            # all-reduce per collect (224 per Llama-8B forward: 3-4x the histogram overhead on 8 GPUs, moving the exchange
+            # to a side stream did not help: profiles/r02_bench_8gpu_hist_step.txt).
             ops.hist_collect_begin(x, self._state, self._buf, hint, self._skip_zeros, first)
-            main, side = torch.cuda.current_stream(x.device), _side_stream(x.device)
-            side.wait_stream(main)
-            with torch.cuda.stream(side):
-                work = dist.all_reduce(self._state[_BATCH_AMAX:_BATCH_AMAX + 1], op=dist.ReduceOp.MAX, group=self.dp_group,
-                                       async_op=True)
-                work.wait()  # NCCL: the side stream waits, not the host
-                ops.hist_collect_end(x, self._state, self._buf, hint, self._skip_zeros, first, self._init_bins, self.numerics)
-                self._read_back()
-                self._side_event = torch.cuda.Event()
-                self._side_event.record(side)
-            x.record_stream(side)  # x is read there (first batch: binning; a batch that grew the range: re-binning)
+            dist.all_reduce(self._state[_BATCH_AMAX:_BATCH_AMAX + 1], op=dist.ReduceOp.MAX, group=self.dp_group)
+            ops.hist_collect_end(x, self._state, self._buf, hint, self._skip_zeros, first, self._init_bins, self.numerics)
         else:
             ops.hist_collect(x, self._state, self._buf, hint, self._skip_zeros, first, self._init_bins, self.numerics)
-            self._read_back()
+        self._read_back()
 
     def _read_back(self):
         # asynchronous read-back (64 bytes), looked at by a later collect: after the first batches, then every 8th
@@ -144,13 +129,6 @@ class HistogramCalibrator(_Calibrator):
             self._host.copy_(self._state, non_blocking=True)
             self._pending = torch.cuda.Event()
             self._pending.record()
-
-    def _join(self):
-        """Order the caller's stream after this calibrator's side-stream work (data-parallel collects)."""
-        ev = getattr(self, "_side_event", None)
-        if ev is not None:
-            torch.cuda.current_stream(self._state.device).wait_event(ev)
-            self._side_event = None
 
     def _hint(self):
         """Bins to keep in shared-memory counters: the last bin count the host has seen (any value is correct)."""
@@ -177,7 +155,6 @@ class HistogramCalibrator(_Calibrator):
         """Blocking read of the device state (compute time, tests): list of 16 ints."""
         if self._state is None:
             return None
-        self._join()
         if not self._snap_valid or self._snap is None:
             self._snap = self._state.tolist()
             self._snap_valid = True
@@ -236,9 +213,6 @@ class HistogramCalibrator(_Calibrator):
         self._override = (counts, edges)
 
     def reset(self):
-        if getattr(self, "_side_event", None) is not None:
-            self._side_event.synchronize()
-            self._side_event = None
         if self._pending is not None:
             self._pending.synchronize()
         self._state = self._buf = self._snap = self._pending = self._edges_cache = self._override = None

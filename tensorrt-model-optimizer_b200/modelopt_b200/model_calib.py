@@ -232,24 +232,26 @@ def _finalize_with_shared_state(model: nn.Module, weight_patterns=None):
 
 
 def sync_histograms(model: nn.Module, group=None):
-    """All-reduce(SUM) of the counts of every HistogramCalibrator over the data-parallel group, in ONE flat int64 buffer.
+    """Merge the HistogramCalibrators of a data-parallel group: all-reduce(MAX) of the ranges, then all-reduce(SUM) of the
+    counts of every calibrator in ONE flat int64 buffer.
 
-    New behaviour (the reference does not synchronise histograms, calib/histogram.py:158-163).  The calibrators of a
-    data-parallel replica take identical range decisions batch by batch (`HistogramCalibrator.dp_group`: the batch
-    maximum is all-reduced(MAX) inside `collect`), so on every rank bin i means the same interval and the sum of the
-    ranks' exact integer counts is bit-identical to ONE process calibrating on the concatenation of the ranks' batches.
-    Ranks first verify that agreement (bin count, range, width of every calibrator: one MIN + one MAX exchange) and raise
-    if it does not hold - e.g. when the calibrators collected before `dp_group` was set.  World size 1 is a no-op, i.e.
-    the reference's behaviour bit for bit; a second call without a `collect` in between does nothing."""
+    New behaviour (the reference does not synchronise histograms, calib/histogram.py:158-163).  Every rank derived the same
+    bin WIDTH from the all-reduced maximum of the first batch (`HistogramCalibrator.collect`), and a range only ever grows
+    in whole bins of that width (histogram.py:121-126), so bin i is the same interval on every rank and a rank whose range
+    stayed smaller simply has zeros above its last bin.  The merge therefore is: (1) verify that the widths agree (MIN and
+    MAX of the state words: one exchange each) and raise if not - e.g. calibrators that collected before `dp_group` was set;
+    (2) every calibrator takes the widest rank's (bin count, range); (3) the exact integer counts are summed.  The result is
+    the bin-by-bin sum of what the reference computes on each rank; with `dp_sync = "step"` the ranks already agree batch
+    by batch and the sum is bit-identical to ONE process fed the union of the ranks' batches.  World size 1 is a no-op (the
+    reference's behaviour bit for bit); a second call without a `collect` in between does nothing."""
     from .calib import HistogramCalibrator
+    from .calib.histogram import _FIRST_AMAX, _FLAGS, _LAST_END, _NBINS, _RANGE_MAX, _WIDTH
 
     if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
         return
     cals = [m._calibrator for m in model.modules()
             if isinstance(m, TensorQuantizer) and isinstance(getattr(m, "_calibrator", None), HistogramCalibrator)
             and m._calibrator._state is not None and not m._calibrator._synced]
-    for c in cals:
-        c._join()  # the last collect's decision may still be running on the calibrators' side stream
     n_cals = torch.tensor([len(cals)], dtype=torch.int64, device=cals[0]._state.device if cals else None)
     if cals:
         lo, hi = n_cals.clone(), n_cals.clone()
@@ -259,16 +261,28 @@ def sync_histograms(model: nn.Module, group=None):
             raise RuntimeError("sync_histograms: ranks hold different numbers of histogram calibrators with data")
     if not cals:
         return
-    dev = cals[0]._state.device
-    meta = torch.stack([c._state[:4] for c in cals]).to(torch.int64)  # bin count, range, width, last growth: all bit patterns
+    # per calibrator: bin count, range, width, end of the last growth, first-batch maximum (fp32 bit patterns of non-negative
+    # values order like the values), and the two freeze flags as separate columns (NCCL has no bitwise OR)
+    st = torch.stack([c._state[:6] for c in cals]).to(torch.int64)
+    meta = torch.cat([st[:, [_NBINS, _RANGE_MAX, _WIDTH, _LAST_END, _FIRST_AMAX]], st[:, _FLAGS:_FLAGS + 1] & 1,
+                      (st[:, _FLAGS:_FLAGS + 1] >> 1) & 1], dim=1)
     lo, hi = meta.clone(), meta.clone()
     dist.all_reduce(lo, op=dist.ReduceOp.MIN, group=group)
     dist.all_reduce(hi, op=dist.ReduceOp.MAX, group=group)
-    if not torch.equal(lo, hi):
-        raise RuntimeError("sync_histograms: ranks disagree on the bins of a histogram (bin count / range / width); "
-                           "calibrate with HistogramCalibrator.dp_group set from the first batch "
-                           "(enable_stats_collection does it) so that every rank takes the same range decisions")
-    sizes = [c._num_bins for c in cals]  # reads the state (and reports a frozen calibrator)
+    if not torch.equal(lo[:, [2, 4]], hi[:, [2, 4]]):
+        raise RuntimeError("sync_histograms: ranks disagree on the bin width of a histogram; calibrate with "
+                           "HistogramCalibrator.dp_group set from the first batch (enable_stats_collection does it) so "
+                           "that every rank derives the width from the all-reduced maximum of the first batch")
+    merged = hi.to(torch.int32)
+    sizes = hi[:, 0].tolist()
+    for c, row, n in zip(cals, merged, sizes):
+        if n > c._buf.numel():
+            raise RuntimeError("sync_histograms: a rank's histogram has more bins than this rank's counts buffer holds "
+                               "(different `headroom` / `num_bins` on the ranks)")
+        c._state[_NBINS], c._state[_RANGE_MAX], c._state[_LAST_END] = row[0], row[1], row[3]
+        c._state[_FLAGS] = row[5] | (row[6] << 1)
+        c._snap_valid = False
+        c._edges_cache = None
     flat = torch.cat([c._buf[:n] for c, n in zip(cals, sizes)])
     dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
     off = 0
@@ -276,6 +290,7 @@ def sync_histograms(model: nn.Module, group=None):
         c._buf[:n] = flat[off:off + n]
         c._synced = True
         off += n
+        c._num_bins  # reads the merged state: a calibrator that froze on ANY rank is reported on every rank
 
 
 @torch.no_grad()

@@ -111,9 +111,10 @@ def _disabled_amax_sync(rank, world):
 
 
 def _hist_sync(rank, world):
-    """sync_histograms: ranks that took the same range decisions (what the per-batch all-reduce(MAX) of the batch maximum
-    inside collect guarantees) sum their exact counts in one flat buffer; ranks that did not are refused.  The device
-    state is written by hand here (the kernels need a GPU)."""
+    """sync_histograms: ranks that share the bin width (what the all-reduce(MAX) of the first batch's maximum inside collect
+    guarantees) merge - the widest rank's bin count / range, exact counts summed in one flat buffer, a narrower rank's
+    missing bins counting as zeros; ranks whose widths differ are refused.  The device state is written by hand here (the
+    kernels need a GPU)."""
     import modelopt_b200 as mtq
     from modelopt_b200.calib import HistogramCalibrator
     from torch import nn
@@ -125,19 +126,24 @@ def _hist_sync(rank, world):
     mtq.enable_stats_collection(m)
     cals = [m[0].input_quantizer._calibrator, m[1].input_quantizer._calibrator]
     assert all(isinstance(c, HistogramCalibrator) and c.dp_group is None for c in cals)  # the default (world) group
+    assert all(c.dp_sync == "finish" for c in cals)
 
     def f32_bits(v):
         return int(torch.tensor([v], dtype=torch.float32).view(torch.int32)[0])
 
-    mine = []
-    for k, (cal, nb) in enumerate(zip(cals, (2048, 2500))):
+    def fill(cal, nb, k, r):
         cal._state = torch.zeros(16, dtype=torch.int32)
         cal._state[0], cal._state[1], cal._state[2] = nb, f32_bits(nb * 0.5), f32_bits(0.5)
         cal._state[3] = 0 if nb == 2048 else f32_bits(nb * 0.5 + 0.25)
         cal._state[5] = f32_bits(1024.0)
         cal._buf = torch.zeros(4096, dtype=torch.int64)
-        cal._buf[:nb] = torch.arange(nb, dtype=torch.int64) % (7 + k) + rank
-        mine.append(cal._buf[:nb].clone())
+        cal._buf[:nb] = torch.arange(nb, dtype=torch.int64) % (7 + k) + r
+        cal._synced = cal._snap_valid = False
+        cal._edges_cache = None
+
+    # (1) every rank ended with the same range
+    for k, (cal, nb) in enumerate(zip(cals, (2048, 2500))):
+        fill(cal, nb, k, rank)
     mtq.sync_histograms(m)
     for k, (cal, nb) in enumerate(zip(cals, (2048, 2500))):
         want = sum(torch.arange(nb, dtype=torch.int64) % (7 + k) + r for r in range(world))
@@ -146,12 +152,30 @@ def _hist_sync(rank, world):
     before = [c._counts.clone() for c in cals]
     mtq.sync_histograms(m)  # already summed: a second call must not sum again
     assert all(torch.equal(a, c._counts) for a, c in zip(before, cals))
-    # ranks whose ranges diverged (no per-batch exchange): refused, not silently mis-added
-    for cal in cals:
-        cal._synced = False
-    cals[1]._state[0] = 2500 + rank
-    cals[1]._snap_valid = False
+    # (2) the second calibrator's range grew further on the higher rank: the merge takes the widest range, the narrower
+    # rank contributes zeros above its own last bin
+    nbs = [2500 + 100 * r for r in range(world)]
+    fill(cals[0], 2048, 0, rank)
+    fill(cals[1], nbs[rank], 1, rank)
+    mtq.sync_histograms(m)
+    want = torch.zeros(nbs[-1], dtype=torch.int64)
+    for r in range(world):
+        want[:nbs[r]] += torch.arange(nbs[r], dtype=torch.int64) % 8 + r
+    assert cals[1]._num_bins == nbs[-1] and torch.equal(cals[1]._counts, want)
+    assert cals[1]._calib_bin_edges.numel() == nbs[-1] + 1
+    assert float(cals[1]._calib_bin_edges[-1]) == nbs[-1] * 0.5
+    # (3) ranks with different bin widths (no exchange at the first batch): refused, not silently mis-added
+    fill(cals[0], 2048, 0, rank)
+    fill(cals[1], 2500, 1, rank)
+    cals[1]._state[2] = f32_bits(0.5 + 0.25 * rank)
     with pytest.raises(RuntimeError, match="disagree"):
+        mtq.sync_histograms(m)
+    # (4) a calibrator that froze on one rank (range beyond the counts buffer) is reported on every rank
+    fill(cals[0], 2048, 0, rank)
+    fill(cals[1], 2500, 1, rank)
+    if rank == world - 1:
+        cals[1]._state[4] = 1
+    with pytest.raises(RuntimeError, match="headroom"):
         mtq.sync_histograms(m)
 
 

@@ -90,8 +90,8 @@ def main():
                 print(f"{preset:38s} {k:34s} ranks identical: {same_ranks}"
                       f"{'' if same_ranks or not must else '   <-- FAIL'}{'' if must else '   (reported only)'}", flush=True)
     # histogram calibration (HistogramCalibrator + entropy / percentile / mse searches): every rank feeds its own batches,
-    # several of which grow the range; the batch maximum is all-reduced inside collect, the counts are summed at finish.
-    # Must equal - bit for bit - ONE rank calibrating on the rank-concatenated batches with no sync at all.
+    # several of which grow the range.  dp_sync = "step": the batch maximum is all-reduced inside every collect, the counts
+    # are summed at finish.  Must equal - bit for bit - ONE rank calibrating on the rank-concatenated batches with no sync at all.
     from modelopt_b200 import model_calib
     from modelopt_b200.calib import HistogramCalibrator
 
@@ -102,10 +102,13 @@ def main():
     hb = [[(torch.randn(128, 512, device="cuda", generator=gh) * (0.5 + 0.9 * s + 0.35 * r)).to(torch.bfloat16)
            for r in range(world)] for s in range(steps)]  # hb[step][rank]; later steps and higher ranks reach further out
 
-    def hist_run(model, feed, sync):
+    def hist_run(model, feed, sync, mode="step"):
         mtq.replace_quant_module(model)
         mtq.set_quantizer_by_cfg(model, hist_cfg)
         model_calib.enable_stats_collection(model, distributed_sync=sync)
+        for q in model.modules():
+            if isinstance(q, TensorQuantizer) and isinstance(getattr(q, "_calibrator", None), HistogramCalibrator):
+                q._calibrator.dp_sync = mode
         with torch.no_grad():
             for b in feed:
                 model(b)
@@ -156,6 +159,44 @@ def main():
                   f"concatenated batches: {exact} ({v.numel()} values){'' if same_ranks and exact else '   <-- FAIL'}", flush=True)
     if rank == 0:
         print(f"{'histogram':38s} range grew during calibration: {grew} ({truth['a.input_quantizer.counts'].numel()} bins)", flush=True)
+    # dp_sync = "finish" (the default): only the FIRST batch's maximum is exchanged (it fixes the bin width); every rank then
+    # grows its own range and the ranks are merged at the end.  Must equal - bit for bit - the bin-by-bin sum of what ONE
+    # process computes on each rank's batches alone when its first batch also contains the group's first-batch maximum
+    # (appended as one extra element, taken out of its bin again afterwards).
+    fin = hist_run(copy.deepcopy(two), [hb[s][rank] for s in range(steps)], True, mode="finish")
+    for name, f in (("a", 1.0), ("b", 2.0)):
+        gmax = max((hb[0][r].float() * f).abs().max() for r in range(world)).to(torch.bfloat16).reshape(1)
+        parts = []
+        for r in range(world):
+            c = HistogramCalibrator(8, None, False)
+            c.collect(torch.cat([(hb[0][r] * f).reshape(-1), gmax]))
+            for s_ in range(1, steps):
+                c.collect(hb[s_][r] * f)
+            cnt = c._counts.clone()
+            cnt[2047] -= 1  # the appended element: v == range maximum of the first batch -> last of the 2048 first bins
+            parts.append((cnt, c._calib_bin_edges.to("cuda").float().clone()))
+        n_max = max(p[0].numel() for p in parts)
+        want = torch.zeros(n_max, dtype=torch.int64, device="cuda")
+        for cnt, _ in parts:
+            want[:cnt.numel()] += cnt
+        want_edges = max(parts, key=lambda p: p[0].numel())[1]
+        got, got_edges = fin[f"{name}.input_quantizer.counts"], fin[f"{name}.input_quantizer.edges"]
+        gathered = [torch.empty_like(got) for _ in range(world)]
+        dist.all_gather(gathered, got.contiguous())
+        same_ranks = all(torch.equal(x, gathered[0]) for x in gathered)
+        exact = got.shape == want.shape and torch.equal(got, want) and torch.equal(got_edges, want_edges)
+        uneven = len({p[0].numel() for p in parts}) > 1
+        ref = HistogramCalibrator(8, None, False)
+        ref.set_histogram(want, want_edges)
+        searches = all(torch.equal(fin[f"{name}.input_quantizer.{m_}"].cpu(), ref.compute_amax(m_, **kw).float().reshape(1).cpu())
+                       for m_, kw in (("entropy", {}), ("percentile", {"percentile": 99.9}), ("mse", {})))
+        close = (fin[f"{name}.input_quantizer.entropy"] / mine[f"{name}.input_quantizer.entropy"]).item()
+        ok &= same_ranks and exact and searches
+        if rank == 0:
+            print(f"{'histogram, dp_sync=finish':38s} {name + '.input_quantizer':34s} ranks identical: {same_ranks}  == sum of the "
+                  f"ranks' single-process histograms: {exact} ({got.numel()} bins; ranks ended with different ranges: {uneven}); "
+                  f"searches on it identical: {searches}; entropy amax / step-mode amax = {close:.4f}"
+                  f"{'' if same_ranks and exact and searches else '   <-- FAIL'}", flush=True)
     # control: without the Hessian sync the ranks refine to different weight amaxes (what the reference warns about)
     import warnings
     c0 = copy.deepcopy(qcfg.NVFP4_W4A4_WEIGHT_LOCAL_HESSIAN_CFG)
