@@ -215,7 +215,7 @@ class HistogramCalibrator(_Calibrator):
     def reset(self):
         if self._pending is not None:
             self._pending.synchronize()
-        self._state = self._buf = self._snap = self._pending = self._edges_cache = self._override = None
+        self._state = self._buf = self._snap = self._pending = self._edges_cache = self._override = self._memo = None
         self._synced = self._snap_valid = False
 
     def compute_amax(self, method: str, *, stride: int = 1, start_bin: int = 128, percentile: float = 99.99,
@@ -228,10 +228,13 @@ class HistogramCalibrator(_Calibrator):
             )
         if self._counts is None and self._calib_bin_edges is None:
             return None
+        memo = getattr(self, "_memo", None)
+        if memo is not None and memo[0] == self._search_key(method, stride, start_bin, percentile):
+            return memo[1].clone()  # finish_stats_collection asks twice (compute_amax, then load_calib_amax), as the reference does
         counts, edges = self._counts, self._calib_bin_edges
         if method == "entropy":
             k = int(ops.hist_entropy_index(counts, self._num_bits, self._unsigned, stride, start_bin))
-            return torch.tensor(edges[start_bin + k * stride].item())
+            return self.finish_search(method, k, stride=stride, start_bin=start_bin, percentile=percentile)
         if method == "mse":
             if self._num_bits == (4, 3) and not intended_mse:
                 # what the reference does (histogram.py:310 passes 4 arguments to a 5-argument function)
@@ -243,8 +246,31 @@ class HistogramCalibrator(_Calibrator):
             return ((e[1:] + e[:-1]) / 2)[i]
         if method == "percentile":
             k = int(ops.hist_percentile_index(counts, percentile))
-            return torch.tensor(edges[k].item())
+            return self.finish_search(method, k, stride=stride, start_bin=start_bin, percentile=percentile)
         raise TypeError(f"Unknown calibration method {method}")
+
+    # ---- the entropy / percentile search in two halves, so that a caller with many calibrators (finish_stats_collection) can
+    # enqueue every search first and read all the indices back with ONE synchronisation ------------------------------------
+    def _search_key(self, method, stride, start_bin, percentile):
+        return (method, stride, start_bin, percentile, getattr(self, "_n_collect", 0), self._synced, id(self._override))
+
+    def launch_search(self, method: str, *, stride: int = 1, start_bin: int = 128, percentile: float = 99.99):
+        """Enqueue the search on the current stream; returns a one-element device tensor (the index) or None (no data)."""
+        counts = self._counts
+        if counts is None:
+            return None
+        if method == "entropy":
+            return ops.hist_entropy_index(counts, self._num_bits, self._unsigned, stride, start_bin)
+        if method == "percentile":
+            return ops.hist_percentile_index(counts, percentile)
+        raise TypeError(f"launch_search: method {method}")
+
+    def finish_search(self, method: str, k: int, *, stride: int = 1, start_bin: int = 128, percentile: float = 99.99):
+        """Index -> amax (what compute_amax returns), remembered until the next collect."""
+        edges = self._calib_bin_edges
+        amax = torch.tensor(edges[start_bin + k * stride if method == "entropy" else k].item())
+        self._memo = (self._search_key(method, stride, start_bin, percentile), amax)
+        return amax.clone()
 
     def __str__(self):
         if self._calib_bin_edges is None:

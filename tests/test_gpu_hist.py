@@ -176,3 +176,36 @@ def test_collect_is_capturable_in_a_cuda_graph(calib):
     graphed.collect(xs[0])          # and the calibrator keeps working eagerly afterwards (read-back included)
     eager.collect(xs[0])
     assert torch.equal(eager._calib_hist, graphed._calib_hist)
+
+
+def test_finish_stats_collection_batches_the_searches():
+    """finish_stats_collection enqueues every calibrator's entropy search on a few streams and reads the indices back once;
+    the amax each quantizer ends up with is the one a lone compute_amax call returns; the two-phase percentile search
+    (launch_search / finish_search) equals compute_amax as well."""
+    import modelopt_b200 as mtq
+    from modelopt_b200 import model_calib
+    from torch import nn
+
+    torch.manual_seed(4)
+    m = nn.Sequential(*[nn.Linear(256, 256) for _ in range(12)]).to("cuda", torch.bfloat16)
+    mtq.replace_quant_module(m)
+    mtq.set_quantizer_by_cfg(m, [{"quantizer_name": "*", "enable": False},
+                                 {"quantizer_name": "*input_quantizer", "cfg": {"num_bits": 8, "calibrator": "histogram"}}])
+    model_calib.enable_stats_collection(m)
+    with torch.no_grad():
+        for s in (1.0, 3.0, 0.5):
+            m(torch.randn(64, 256, device="cuda", dtype=torch.bfloat16) * s)
+    model_calib.finish_stats_collection(m, "entropy")
+    for lin in m:
+        q = lin.input_quantizer
+        cal = q._calibrator
+        assert cal._memo is not None
+        cal._memo = None
+        lone = cal.compute_amax("entropy")
+        assert float(q._amax) == float(lone) and float(lone) > 0
+        cal._memo = None
+        k = int(cal.launch_search("percentile", percentile=99.9))
+        two_phase = cal.finish_search("percentile", k, percentile=99.9)
+        assert float(cal.compute_amax("percentile", percentile=99.9)) == float(two_phase)   # served from the memo
+        cal._memo = None
+        assert float(cal.compute_amax("percentile", percentile=99.9)) == float(two_phase)   # and computed afresh
