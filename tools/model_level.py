@@ -358,7 +358,7 @@ def run(model_name="8b", presets=("nvfp4",), n_seq_total=512, micro_batch=8, seq
             "scaling": "strong",
             "plain_gemm_backend": ops.PLAIN_GEMM["backend"],
         }
-        del model, feeder, quantizers, enabled, with_amax
+        del model, feeder, quantizers, enabled, with_amax, tiny  # `tiny` holds the model in a default argument
         gc.collect()
         torch.cuda.empty_cache()
     return out
