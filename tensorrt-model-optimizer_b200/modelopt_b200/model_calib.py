@@ -326,14 +326,16 @@ def sync_histograms(model: nn.Module, group=None):
         raise RuntimeError("sync_histograms: ranks disagree on the bin width of a histogram; calibrate with "
                            "HistogramCalibrator.dp_group set from the first batch (enable_stats_collection does it) so "
                            "that every rank derives the width from the all-reduced maximum of the first batch")
-    merged = hi.to(torch.int32)
-    sizes = hi[:, 0].tolist()
-    for c, row, n in zip(cals, merged, sizes):
+    own, merged = meta.tolist(), hi.tolist()  # two host reads for all calibrators
+    sizes = [row[0] for row in merged]
+    for c, mine, row, n in zip(cals, own, merged, sizes):
         if n > c._buf.numel():
             raise RuntimeError("sync_histograms: a rank's histogram has more bins than this rank's counts buffer holds "
                                "(different `headroom` / `num_bins` on the ranks)")
-        c._state[_NBINS], c._state[_RANGE_MAX], c._state[_LAST_END] = row[0], row[1], row[3]
-        c._state[_FLAGS] = row[5] | (row[6] << 1)
+        if mine != row:  # another rank's range grew further, or a rank froze: take over the merged state
+            st_new = c._state.tolist()
+            st_new[_NBINS], st_new[_RANGE_MAX], st_new[_LAST_END], st_new[_FLAGS] = row[0], row[1], row[3], row[5] | (row[6] << 1)
+            c._state.copy_(torch.tensor(st_new, dtype=torch.int32))
         c._snap_valid = False
         c._edges_cache = None
     flat = torch.cat([c._buf[:n] for c, n in zip(cals, sizes)])
