@@ -62,6 +62,8 @@ class HistogramCalibrator(_Calibrator):
         self._edges_cache = None
         self._override = None   # (counts, edges) set by hand (tests, external restore)
         self._synced = False    # counts already summed over the data-parallel group
+        self._n_collect = 0     # collects so far (paces the state read-back, invalidates remembered search results)
+        self._memo = None       # (search key, amax) of the last entropy / percentile search
         self._torch_hist = torch_hist
         # data-parallel group whose ranks calibrate together: False = none; None = the default (world) group
         self.dp_group = False
@@ -102,7 +104,7 @@ class HistogramCalibrator(_Calibrator):
         self._synced = False
         self._edges_cache = None
         self._snap_valid = False
-        self._n_collect = getattr(self, "_n_collect", 0) + 1
+        self._n_collect += 1
         if self._group_size() > 1 and (first or self.dp_sync == "step"):
             # Data-parallel.  The FIRST batch's maximum is all-reduced(MAX): it fixes the bin width, which must be the same on
             # every rank for the counts to be summable at the end.  dp_sync == "finish" (default): later batches are collected
@@ -217,6 +219,7 @@ class HistogramCalibrator(_Calibrator):
             self._pending.synchronize()
         self._state = self._buf = self._snap = self._pending = self._edges_cache = self._override = self._memo = None
         self._synced = self._snap_valid = False
+        self._n_collect = 0
 
     def compute_amax(self, method: str, *, stride: int = 1, start_bin: int = 128, percentile: float = 99.99,
                      intended_mse: bool = False):
@@ -228,7 +231,7 @@ class HistogramCalibrator(_Calibrator):
             )
         if self._counts is None and self._calib_bin_edges is None:
             return None
-        memo = getattr(self, "_memo", None)
+        memo = self._memo
         if memo is not None and memo[0] == self._search_key(method, stride, start_bin, percentile):
             return memo[1].clone()  # finish_stats_collection asks twice (compute_amax, then load_calib_amax), as the reference does
         counts, edges = self._counts, self._calib_bin_edges
@@ -252,7 +255,7 @@ class HistogramCalibrator(_Calibrator):
     # ---- the entropy / percentile search in two halves, so that a caller with many calibrators (finish_stats_collection) can
     # enqueue every search first and read all the indices back with ONE synchronisation ------------------------------------
     def _search_key(self, method, stride, start_bin, percentile):
-        return (method, stride, start_bin, percentile, getattr(self, "_n_collect", 0), self._synced, id(self._override))
+        return (method, stride, start_bin, percentile, self._n_collect, self._synced, id(self._override))
 
     def launch_search(self, method: str, *, stride: int = 1, start_bin: int = 128, percentile: float = 99.99):
         """Enqueue the search on the current stream; returns a one-element device tensor (the index) or None (no data)."""
